@@ -1,0 +1,451 @@
+/*
+ * nmpc_oracle_qp.c -- CPU ORACLE (test infrastructure, NOT the product).  See nmpc_oracle.h.
+ * PARITY UNPINNED.  QP assembly (acados LINEAR_LS + Gauss-Newton + LM, delta form) and a
+ * box-constrained Riccati interior-point solver standing in for HPIPM
+ * (controller.py:181-185; HPIPM itself is un-vendored).  The QP is strictly convex, so
+ * its primal optimum is unique and any tightly converged solver pins it.
+ */
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "nmpc_oracle.h"
+
+#define NX ORC_NX
+#define NU ORC_NU
+#define NZ ORC_NZ
+
+orc_qp *orc_qp_alloc(int N) {
+  orc_qp *qp = (orc_qp *)calloc(1, sizeof(orc_qp));
+  qp->N = N;
+  qp->A = (double *)calloc((size_t)N * NX * NX, sizeof(double));
+  qp->B = (double *)calloc((size_t)N * NX * NU, sizeof(double));
+  qp->b = (double *)calloc((size_t)N * NX, sizeof(double));
+  qp->Q = (double *)calloc((size_t)(N + 1) * NX, sizeof(double));
+  qp->R = (double *)calloc((size_t)N * NU, sizeof(double));
+  qp->q = (double *)calloc((size_t)(N + 1) * NX, sizeof(double));
+  qp->r = (double *)calloc((size_t)N * NU, sizeof(double));
+  qp->lb = (double *)calloc((size_t)N * NU, sizeof(double));
+  qp->ub = (double *)calloc((size_t)N * NU, sizeof(double));
+  return qp;
+}
+
+void orc_qp_free(orc_qp *qp) {
+  if (!qp) return;
+  free(qp->A);
+  free(qp->B);
+  free(qp->b);
+  free(qp->Q);
+  free(qp->R);
+  free(qp->q);
+  free(qp->r);
+  free(qp->lb);
+  free(qp->ub);
+  free(qp);
+}
+
+/* controller.py:223-245 (LINEAR_LS, y=[x;u]), :189-190 (LM), :248-250 (u box);
+ * UPSTREAM acados: stage cost scaled by the time step, terminal by 1. */
+void orc_build_qp(const orc_config *c, const double *xtraj, const double *utraj,
+                  const double *yref, const double *yref_e, orc_qp *qp) {
+  const int N = c->N;
+  const double sc = c->cost_scale_dt ? c->dt : 1.0;
+  const double lm_s = c->lm_scaled_by_dt ? c->lm * c->dt : c->lm;
+  for (int k = 0; k < N; k++) {
+    const double *x = xtraj + (size_t)k * NX;
+    const double *u = utraj + (size_t)k * NU;
+    double xn[NX];
+    orc_discretize(c, x, u, xn, qp->A + (size_t)k * NX * NX, qp->B + (size_t)k * NX * NU);
+    for (int i = 0; i < NX; i++) {
+      qp->b[k * NX + i] = xn[i] - xtraj[(size_t)(k + 1) * NX + i];
+      qp->Q[k * NX + i] = sc * c->W[i] + lm_s;
+      qp->q[k * NX + i] = sc * c->W[i] * (x[i] - yref[(size_t)k * NZ + i]);
+    }
+    for (int i = 0; i < NU; i++) {
+      qp->R[k * NU + i] = sc * c->W[NX + i] + lm_s;
+      qp->r[k * NU + i] = sc * c->W[NX + i] * (u[i] - yref[(size_t)k * NZ + NX + i]);
+      qp->lb[k * NU + i] = c->lbu[i] - u[i];
+      qp->ub[k * NU + i] = c->ubu[i] - u[i];
+    }
+  }
+  const double *xN = xtraj + (size_t)N * NX;
+  for (int i = 0; i < NX; i++) {
+    qp->Q[N * NX + i] = c->We[i] + c->lm;
+    qp->q[N * NX + i] = c->We[i] * (xN[i] - yref_e[i]);
+  }
+}
+
+/* ---------------------------------------------------------------- Riccati */
+typedef struct {
+  int N;
+  double *K;    /* N*4*13 feedback */
+  double *Qi;   /* N*16  inverse of Quu */
+  double *kff;  /* N*4 */
+} ric_ws;
+
+static int chol4_inv(const double *G, double *Ginv) {
+  /* inverse of a symmetric positive definite 4x4 via Cholesky */
+  double L[16] = {0};
+  for (int j = 0; j < 4; j++) {
+    double d = G[j * 4 + j];
+    for (int k = 0; k < j; k++) d -= L[j * 4 + k] * L[j * 4 + k];
+    if (!(d > 0.0)) return 1;
+    L[j * 4 + j] = sqrt(d);
+    for (int i = j + 1; i < 4; i++) {
+      double s = G[i * 4 + j];
+      for (int k = 0; k < j; k++) s -= L[i * 4 + k] * L[j * 4 + k];
+      L[i * 4 + j] = s / L[j * 4 + j];
+    }
+  }
+  /* Linv */
+  double Li[16] = {0};
+  for (int j = 0; j < 4; j++) {
+    Li[j * 4 + j] = 1.0 / L[j * 4 + j];
+    for (int i = j + 1; i < 4; i++) {
+      double s = 0.0;
+      for (int k = j; k < i; k++) s -= L[i * 4 + k] * Li[k * 4 + j];
+      Li[i * 4 + j] = s / L[i * 4 + i];
+    }
+  }
+  for (int i = 0; i < 4; i++)
+    for (int j = 0; j < 4; j++) {
+      double s = 0.0;
+      for (int k = 0; k < 4; k++) s += Li[k * 4 + i] * Li[k * 4 + j];
+      Ginv[i * 4 + j] = s;
+    }
+  return 0;
+}
+
+/* Backward factorisation with modified input Hessian Rt and gradient rt, fused with the
+ * right-hand side (rho*b, rho*q, rt); forward roll-out from dx_0 = 0.  Returns non-zero on breakdown. */
+static int riccati_factor_solve(const orc_qp *qp, double rho, const double *Rt, const double *rt,
+                                ric_ws *ws, double *dx, double *du) {
+  const int N = qp->N;
+  double P[NX * NX] = {0}, p[NX];
+  for (int i = 0; i < NX; i++) {
+    P[i * NX + i] = qp->Q[N * NX + i];
+    p[i] = rho * qp->q[N * NX + i];
+  }
+  for (int k = N - 1; k >= 0; k--) {
+    const double *A = qp->A + (size_t)k * NX * NX;
+    const double *B = qp->B + (size_t)k * NX * NU;
+    const double *b = qp->b + (size_t)k * NX;
+    double PA[NX * NX], PB[NX * NU], w[NX];
+    for (int i = 0; i < NX; i++) {
+      for (int j = 0; j < NX; j++) {
+        double s = 0;
+        for (int l = 0; l < NX; l++) s += P[i * NX + l] * A[l * NX + j];
+        PA[i * NX + j] = s;
+      }
+      for (int j = 0; j < NU; j++) {
+        double s = 0;
+        for (int l = 0; l < NX; l++) s += P[i * NX + l] * B[l * NU + j];
+        PB[i * NU + j] = s;
+      }
+      double s = p[i];
+      for (int l = 0; l < NX; l++) s += P[i * NX + l] * (rho * b[l]);
+      w[i] = s;
+    }
+    double Quu[16], Qux[NU * NX], Qxx[NX * NX], gu[NU], gx[NX];
+    for (int i = 0; i < NU; i++) {
+      for (int j = 0; j < NU; j++) {
+        double s = (i == j) ? Rt[k * NU + i] : 0.0;
+        for (int l = 0; l < NX; l++) s += B[l * NU + i] * PB[l * NU + j];
+        Quu[i * 4 + j] = s;
+      }
+      for (int j = 0; j < NX; j++) {
+        double s = 0;
+        for (int l = 0; l < NX; l++) s += B[l * NU + i] * PA[l * NX + j];
+        Qux[i * NX + j] = s;
+      }
+      double s = rt[k * NU + i];
+      for (int l = 0; l < NX; l++) s += B[l * NU + i] * w[l];
+      gu[i] = s;
+    }
+    for (int i = 0; i < NX; i++) {
+      for (int j = 0; j < NX; j++) {
+        double s = (i == j) ? qp->Q[k * NX + i] : 0.0;
+        for (int l = 0; l < NX; l++) s += A[l * NX + i] * PA[l * NX + j];
+        Qxx[i * NX + j] = s;
+      }
+      double s = rho * qp->q[k * NX + i];
+      for (int l = 0; l < NX; l++) s += A[l * NX + i] * w[l];
+      gx[i] = s;
+    }
+    double *Qi = ws->Qi + (size_t)k * 16;
+    if (chol4_inv(Quu, Qi)) return 1;
+    double *K = ws->K + (size_t)k * NU * NX;
+    double *kff = ws->kff + (size_t)k * NU;
+    for (int i = 0; i < NU; i++) {
+      for (int j = 0; j < NX; j++) {
+        double s = 0;
+        for (int l = 0; l < NU; l++) s -= Qi[i * 4 + l] * Qux[l * NX + j];
+        K[i * NX + j] = s;
+      }
+      double s = 0;
+      for (int l = 0; l < NU; l++) s -= Qi[i * 4 + l] * gu[l];
+      kff[i] = s;
+    }
+    for (int i = 0; i < NX; i++) {
+      for (int j = 0; j < NX; j++) {
+        double s = Qxx[i * NX + j];
+        for (int l = 0; l < NU; l++) s += Qux[l * NX + i] * K[l * NX + j];
+        P[i * NX + j] = s;
+      }
+      double s = gx[i];
+      for (int l = 0; l < NU; l++) s += Qux[l * NX + i] * kff[l];
+      p[i] = s;
+    }
+    /* symmetrise */
+    for (int i = 0; i < NX; i++)
+      for (int j = i + 1; j < NX; j++) {
+        const double m = 0.5 * (P[i * NX + j] + P[j * NX + i]);
+        P[i * NX + j] = P[j * NX + i] = m;
+      }
+  }
+  memset(dx, 0, sizeof(double) * NX);
+  for (int k = 0; k < N; k++) {
+    const double *A = qp->A + (size_t)k * NX * NX;
+    const double *B = qp->B + (size_t)k * NX * NU;
+    const double *K = ws->K + (size_t)k * NU * NX;
+    const double *x = dx + (size_t)k * NX;
+    double *u = du + (size_t)k * NU;
+    double *xn = dx + (size_t)(k + 1) * NX;
+    for (int i = 0; i < NU; i++) {
+      double s = ws->kff[k * NU + i];
+      for (int j = 0; j < NX; j++) s += K[i * NX + j] * x[j];
+      u[i] = s;
+    }
+    for (int i = 0; i < NX; i++) {
+      double s = rho * qp->b[k * NX + i];
+      for (int j = 0; j < NX; j++) s += A[i * NX + j] * x[j];
+      for (int j = 0; j < NU; j++) s += B[i * NU + j] * u[j];
+      xn[i] = s;
+    }
+  }
+  return 0;
+}
+
+/* Re-solve with the same factorisation for a right-hand side that differs only in the
+ * input gradient (b = 0, q = 0, r = dr): the corrector increment of Mehrotra's method. */
+static void riccati_delta_solve(const orc_qp *qp, const double *dr, const ric_ws *ws, double *dx,
+                                double *du, double *kffd) {
+  const int N = qp->N;
+  double p[NX] = {0};
+  for (int k = N - 1; k >= 0; k--) {
+    const double *A = qp->A + (size_t)k * NX * NX;
+    const double *B = qp->B + (size_t)k * NX * NU;
+    const double *K = ws->K + (size_t)k * NU * NX;
+    const double *Qi = ws->Qi + (size_t)k * 16;
+    double gu[NU], gx[NX];
+    for (int i = 0; i < NU; i++) {
+      double s = dr[k * NU + i];
+      for (int l = 0; l < NX; l++) s += B[l * NU + i] * p[l];
+      gu[i] = s;
+    }
+    for (int i = 0; i < NX; i++) {
+      double s = 0;
+      for (int l = 0; l < NX; l++) s += A[l * NX + i] * p[l];
+      gx[i] = s;
+    }
+    for (int i = 0; i < NU; i++) {
+      double s = 0;
+      for (int l = 0; l < NU; l++) s -= Qi[i * 4 + l] * gu[l];
+      kffd[k * NU + i] = s;
+    }
+    for (int i = 0; i < NX; i++) {
+      double s = gx[i];
+      for (int l = 0; l < NU; l++) s += K[l * NX + i] * gu[l];
+      p[i] = s;
+    }
+  }
+  memset(dx, 0, sizeof(double) * NX);
+  for (int k = 0; k < N; k++) {
+    const double *A = qp->A + (size_t)k * NX * NX;
+    const double *B = qp->B + (size_t)k * NX * NU;
+    const double *K = ws->K + (size_t)k * NU * NX;
+    const double *x = dx + (size_t)k * NX;
+    double *u = du + (size_t)k * NU;
+    double *xn = dx + (size_t)(k + 1) * NX;
+    for (int i = 0; i < NU; i++) {
+      double s = kffd[k * NU + i];
+      for (int j = 0; j < NX; j++) s += K[i * NX + j] * x[j];
+      u[i] = s;
+    }
+    for (int i = 0; i < NX; i++) {
+      double s = 0;
+      for (int j = 0; j < NX; j++) s += A[i * NX + j] * x[j];
+      for (int j = 0; j < NU; j++) s += B[i * NU + j] * u[j];
+      xn[i] = s;
+    }
+  }
+}
+
+/* ------------------------------------------------------- interior point */
+/* Mehrotra predictor-corrector on
+ *     min 1/2 z'Hz + g'z   s.t. dynamics,  lb <= du <= ub
+ * with slacks t_l = du - lb, t_u = ub - du and multipliers lam_l, lam_u >= 0.
+ *
+ * One step length is used for primal and dual variables, so every *linear* residual
+ * (dynamics, box, stationarity) of the iterate equals rho = prod(1 - alpha) times its value
+ * at the starting point (dz = 0, pi = 0), which is plain problem data:
+ *     dynamics b,  x-stationarity q,  u-stationarity ru0 = r - lam_l0 + lam_u0,
+ *     box rbl0 = -lb - t_l0,  rbu0 = ub - t_u0.
+ * The Newton step is therefore computed from right-hand sides that shrink with the
+ * iterate (no cancellation, no costates needed):
+ *     Rt = R + lam_l/t_l + lam_u/t_u
+ *     rt = rho ru0 + d_l rho rbl0 + lam_l - d_u rho rbu0 - lam_u - s_l/t_l + s_u/t_u ,
+ *     s  = sigma*mu - (dt_aff * dlam_aff)          (0 for the predictor)
+ *     Riccati solve with (rho b, rho q, rt)  ->  (Dx, Du)
+ * Predictor and corrector share the factorisation and differ only in rt, so the
+ * corrector is a vector-only re-solve added to the predictor direction. */
+int orc_qp_solve(const orc_qp *qp, int iter_max, double tol, double *dx, double *du, double *lam_l,
+                 double *lam_u, int *iters) {
+  const int N = qp->N;
+  const int nb = N * NU;
+  ric_ws ws;
+  ws.N = N;
+  ws.K = (double *)malloc(sizeof(double) * (size_t)N * NU * NX);
+  ws.Qi = (double *)malloc(sizeof(double) * (size_t)N * 16);
+  ws.kff = (double *)malloc(sizeof(double) * (size_t)N * NU);
+  double *buf = (double *)calloc((size_t)nb * 15 + (size_t)(N + 1) * NX * 2, sizeof(double));
+  double *t_l = buf, *t_u = t_l + nb, *Rt = t_u + nb, *rt = Rt + nb;
+  double *dtl = rt + nb, *dtu = dtl + nb, *dll = dtu + nb, *dlu = dll + nb;
+  double *dr = dlu + nb, *ua = dr + nb, *uc = ua + nb, *kffd = uc + nb;
+  double *rbl0 = kffd + nb, *rbu0 = rbl0 + nb, *ru0 = rbu0 + nb;
+  double *xa = ru0 + nb, *xc = xa + (size_t)(N + 1) * NX;
+  int status = ORC_MAXITER;
+  int it = 0;
+
+  /* Phase 0: equality-constrained QP (box ignored).  If its solution respects the box it
+   * is the QP solution (strict convexity) and no interior-point iteration is needed. */
+  double res0 = 0.0;
+  for (int i = 0; i < nb; i++) res0 = fmax(res0, fabs(qp->r[i]) + fabs(qp->lb[i]) + fabs(qp->ub[i]));
+  for (int i = 0; i < N * NX; i++) res0 = fmax(res0, fabs(qp->b[i]));
+  for (int i = 0; i < (N + 1) * NX; i++) res0 = fmax(res0, fabs(qp->q[i]));
+  if (!(res0 == res0) || isinf(res0)) { /* NaN/Inf in the QP data */
+    status = ORC_QP_FAILURE;
+    goto done;
+  }
+  if (riccati_factor_solve(qp, 1.0, qp->R, qp->r, &ws, dx, du)) {
+    status = ORC_QP_FAILURE;
+    goto done;
+  }
+  {
+    int feasible = 1;
+    for (int i = 0; i < nb; i++)
+      if (!(du[i] >= qp->lb[i] && du[i] <= qp->ub[i])) feasible = 0;
+    if (feasible) {
+      for (int i = 0; i < nb; i++) lam_l[i] = lam_u[i] = 0.0;
+      status = ORC_SUCCESS;
+      goto done;
+    }
+  }
+  /* Interior-point start: the unconstrained solution (dynamics and x-stationarity hold
+   * exactly there), slacks clipped away from zero, lam = mu0 / t. */
+  const double thr0 = 0.1, mu0 = 0.1;
+  res0 = 0.0;
+  for (int i = 0; i < nb; i++) {
+    t_l[i] = fmax(du[i] - qp->lb[i], thr0);
+    t_u[i] = fmax(qp->ub[i] - du[i], thr0);
+    lam_l[i] = mu0 / t_l[i];
+    lam_u[i] = mu0 / t_u[i];
+    rbl0[i] = du[i] - qp->lb[i] - t_l[i];
+    rbu0[i] = qp->ub[i] - du[i] - t_u[i];
+    ru0[i] = -lam_l[i] + lam_u[i];
+    res0 = fmax(res0, fmax(fabs(rbl0[i]), fabs(rbu0[i])));
+    res0 = fmax(res0, fabs(ru0[i]));
+  }
+  it = 1;
+  double rho = 1.0;
+
+  for (; it < iter_max; it++) {
+    double mu = 0.0;
+    for (int i = 0; i < nb; i++) mu += t_l[i] * lam_l[i] + t_u[i] * lam_u[i];
+    mu /= (double)(2 * nb);
+    if (!(mu == mu)) {
+      status = ORC_QP_FAILURE;
+      break;
+    }
+    if (mu <= tol && rho * res0 <= tol) {
+      status = ORC_SUCCESS;
+      break;
+    }
+    /* predictor */
+    for (int i = 0; i < nb; i++) {
+      const double dl = lam_l[i] / t_l[i], dw = lam_u[i] / t_u[i];
+      Rt[i] = qp->R[i] + dl + dw;
+      rt[i] = rho * ru0[i] + dl * (rho * rbl0[i]) + lam_l[i] - dw * (rho * rbu0[i]) - lam_u[i];
+    }
+    if (riccati_factor_solve(qp, 0.0, Rt, rt, &ws, xa, ua)) {
+      status = ORC_QP_FAILURE;
+      break;
+    }
+    double alpha_aff = 1.0;
+    for (int i = 0; i < nb; i++) {
+      dtl[i] = ua[i] + rho * rbl0[i];
+      dtu[i] = -ua[i] + rho * rbu0[i];
+      dll[i] = -(lam_l[i] / t_l[i]) * dtl[i] - lam_l[i];
+      dlu[i] = -(lam_u[i] / t_u[i]) * dtu[i] - lam_u[i];
+      if (dtl[i] < 0) alpha_aff = fmin(alpha_aff, -t_l[i] / dtl[i]);
+      if (dtu[i] < 0) alpha_aff = fmin(alpha_aff, -t_u[i] / dtu[i]);
+      if (dll[i] < 0) alpha_aff = fmin(alpha_aff, -lam_l[i] / dll[i]);
+      if (dlu[i] < 0) alpha_aff = fmin(alpha_aff, -lam_u[i] / dlu[i]);
+    }
+    double mu_aff = 0.0;
+    for (int i = 0; i < nb; i++)
+      mu_aff += (t_l[i] + alpha_aff * dtl[i]) * (lam_l[i] + alpha_aff * dll[i]) +
+                (t_u[i] + alpha_aff * dtu[i]) * (lam_u[i] + alpha_aff * dlu[i]);
+    mu_aff /= (double)(2 * nb);
+    double sigma = mu_aff / mu;
+    sigma = sigma * sigma * sigma;
+    /* corrector increment: only the input gradient changes */
+    for (int i = 0; i < nb; i++) {
+      const double sl = sigma * mu - dtl[i] * dll[i];
+      const double su = sigma * mu - dtu[i] * dlu[i];
+      dr[i] = -sl / t_l[i] + su / t_u[i];
+    }
+    riccati_delta_solve(qp, dr, &ws, xc, uc, kffd);
+    double alpha = 1e300; /* longest step keeping t, lam >= 0 (not capped at 1 yet) */
+    for (int i = 0; i < nb; i++) {
+      const double un = ua[i] + uc[i];
+      const double sl = sigma * mu - dtl[i] * dll[i];
+      const double su = sigma * mu - dtu[i] * dlu[i];
+      dtl[i] = un + rho * rbl0[i];
+      dtu[i] = -un + rho * rbu0[i];
+      dll[i] = -(lam_l[i] / t_l[i]) * dtl[i] + sl / t_l[i] - lam_l[i];
+      dlu[i] = -(lam_u[i] / t_u[i]) * dtu[i] + su / t_u[i] - lam_u[i];
+      if (dtl[i] < 0) alpha = fmin(alpha, -t_l[i] / dtl[i]);
+      if (dtu[i] < 0) alpha = fmin(alpha, -t_u[i] / dtu[i]);
+      if (dll[i] < 0) alpha = fmin(alpha, -lam_l[i] / dll[i]);
+      if (dlu[i] < 0) alpha = fmin(alpha, -lam_u[i] / dlu[i]);
+    }
+    if (!(alpha == alpha)) {
+      status = ORC_QP_FAILURE;
+      break;
+    }
+    /* fraction to the boundary, then cap at the full Newton step */
+    const double tau = fmax(0.995, 1.0 - mu);
+    alpha = fmin(1.0, tau * alpha);
+    if (alpha < 1e-12) {
+      status = ORC_MINSTEP;
+      break;
+    }
+    for (int i = 0; i < nb; i++) {
+      du[i] += alpha * (ua[i] + uc[i]);
+      t_l[i] += alpha * dtl[i];
+      t_u[i] += alpha * dtu[i];
+      lam_l[i] += alpha * dll[i];
+      lam_u[i] += alpha * dlu[i];
+    }
+    for (int i = 0; i < (N + 1) * NX; i++) dx[i] += alpha * (xa[i] + xc[i]);
+    rho *= (1.0 - alpha);
+  }
+done:
+  if (iters) *iters = it;
+  free(buf);
+  free(ws.K);
+  free(ws.Qi);
+  free(ws.kff);
+  return status;
+}
