@@ -1,0 +1,144 @@
+/*
+ * nmpc_b200.h -- C ABI of the B200-native batched NMPC solver (libnmpc_b200.so).
+ *
+ * Drop-in boundary for what the reference's PositionNMPC obtains from acados'
+ * generated solver through ctypes (`AcadosOcpSolver` create / set / solve / get):
+ *   /root/reference/src/rotors_mpc_controller/controller.py
+ *     :175-264  _create_solver  (OCP description -> codegen -> .so -> *_acados_create)
+ *     :414-445  solver.set(stage, 'lbx'|'ubx'|'x'|'u'|'yref', ...)   64 calls / solve
+ *     :447      solver.solve()
+ *     :452-460  solver.get(stage, 'u'|'x')                             42 calls / solve
+ *   /root/reference/nodes/mpc_controller_node:124-131,152-164  (command map + fail-safe)
+ *
+ * Plain pointers and sizes only; no torch / CUDA types in the signatures (a stream is
+ * passed as void*).  All functions return 0 on success or a negative NMPC_E_* code and
+ * never throw.  Per-problem solver status is DATA (int32[batch], acados-style codes).
+ * A handle is bound to one CUDA device and is not thread-safe (the reference serialises
+ * solve/reconfigure with a lock: nodes/mpc_controller_node:58,122,193).
+ */
+#ifndef NMPC_B200_H
+#define NMPC_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NMPC_NX 13
+#define NMPC_NU 4
+#define NMPC_NY 17
+
+/* API error codes (function return values) */
+#define NMPC_OK 0
+#define NMPC_E_INVALID (-1)   /* bad argument / unsupported configuration */
+#define NMPC_E_CUDA (-2)      /* CUDA runtime error (see nmpc_last_error) */
+#define NMPC_E_NOMEM (-3)
+#define NMPC_E_NODEVICE (-4)  /* no CUDA device: there is NO CPU fallback */
+
+/* per-problem solver status (acados enum; controller.py:448 tests `status != 0`) */
+#define NMPC_STATUS_SUCCESS 0
+#define NMPC_STATUS_NAN 1
+#define NMPC_STATUS_MAXITER 2
+#define NMPC_STATUS_MINSTEP 3
+#define NMPC_STATUS_QP_FAILURE 4
+
+#define NMPC_PRECISION_F64 0
+#define NMPC_PRECISION_F32 1
+
+/* Solver constants: the reference's ControllerParams (controller.py:24-49) and the acados
+ * options of controller.py:179-190 made explicit.  Replaces the AcadosOcp description +
+ * generated C code: no code generation or compiler is involved at run time. */
+typedef struct nmpc_config {
+  int32_t N;               /* horizon_steps (1..600, cfg/rotors_mpc.cfg:9) */
+  int32_t qp_iter_max;     /* iter_max -> qp_solver_iter_max (controller.py:185) */
+  int32_t integ_ns;        /* sim_method_num_stages: 1 Euler, 2 midpoint (ref), 4 RK4 */
+  int32_t integ_steps;     /* sim_method_num_steps (ref: 2) */
+  int32_t cost_scale_dt;   /* stage cost scaled by dt (acados default: 1) */
+  int32_t lm_scaled_by_dt; /* LM term scaled by dt (default 0) */
+  int32_t max_sqp_iter;    /* 1 = SQP_RTI (reference); >1 = SQP until step <= sqp_tol */
+  int32_t nan_status;      /* status reported when NaNs appear in the iterate (4 or 1) */
+  int32_t precision;       /* NMPC_PRECISION_F64 | NMPC_PRECISION_F32 */
+  int32_t reserved;
+  double dt;
+  double W[17];            /* stage weights [p(3) v(3) q(4) w(3) u(4)] (controller.py:234-240) */
+  double We[13];           /* terminal weights (controller.py:241) */
+  double lm;               /* levenberg_marquardt (controller.py:190) */
+  double mass;
+  double J[3];             /* inertia diagonal (controller.py:81-83) */
+  double gravity;
+  double rotor_x[4];       /* controller.py:100 */
+  double rotor_y[4];       /* controller.py:101 */
+  double rotor_z[4];       /* spin * km (controller.py:102-103) */
+  double lbu[4];           /* controller.py:105-110, 248-250 */
+  double ubu[4];
+  double kf;               /* rotor_force_constant */
+  double w_min;            /* motor_min_speed */
+  double w_max;            /* motor_max_speed */
+  double sqp_tol;          /* inf-norm step tolerance when max_sqp_iter > 1 */
+  double ipm_tol;          /* interior-point complementarity / residual tolerance */
+} nmpc_config_t;
+
+typedef struct nmpc_handle nmpc_handle_t;
+
+/* Replaces AcadosOcpSolver(ocp, json_file=...) (controller.py:263): allocates the device
+ * workspace, warm-start store (x:(N+1,13), u:(N,4) per problem, controller.py:163-167), the
+ * valid mask (False) and the last-valid command (hover thrust, mpc_controller_node:64). */
+int nmpc_create(const nmpc_config_t *cfg, int32_t batch, int32_t device, nmpc_handle_t **out);
+int nmpc_destroy(nmpc_handle_t *h);
+
+/* Swap constants without re-allocating (same N / precision): the counterpart of building a new
+ * PositionNMPC on every dynamic-reconfigure event (mpc_controller_node:196-198).  Invalidates
+ * the warm start like controller.py:163-167. */
+int nmpc_reconfigure(nmpc_handle_t *h, const nmpc_config_t *cfg);
+
+/* Override the input box (default: controller.py:105-110). */
+int nmpc_set_bounds(nmpc_handle_t *h, const double lbu[4], const double ubu[4]);
+
+/* _prev_solution_valid = False for problems with mask[i] != 0 (all when mask == NULL);
+ * host pointer. */
+int nmpc_invalidate(nmpc_handle_t *h, const uint8_t *mask);
+/* Reset the last-valid command to hover thrust (all problems). */
+int nmpc_reset_last_command(nmpc_handle_t *h);
+
+/* One PositionNMPC.solve() per problem + the node's command mapping, inputs and outputs in
+ * DEVICE memory (FP64 regardless of compute precision):
+ *   x0[batch,13] (quaternion already normalised, controller.py:406-411)
+ *   yref[batch,N,17], yref_e[batch,13]                   (controller.py:433-445)
+ *   u0[batch,4], status[batch] (int32), thrust[batch,4], speed[batch,4]; any output may be NULL.
+ * Asynchronous on `stream` (a cudaStream_t, NULL = default stream). */
+int nmpc_solve_device(nmpc_handle_t *h, const double *x0, const double *yref, const double *yref_e,
+                      double *u0, int32_t *status, double *thrust, double *speed, void *stream);
+
+/* Same with HOST buffers (pinned or pageable): H2D copies, solve, D2H copies, stream sync. */
+int nmpc_solve_host(nmpc_handle_t *h, const double *x0, const double *yref, const double *yref_e,
+                    double *u0, int32_t *status, double *thrust, double *speed);
+
+/* Copy out the warm-start store / statistics (dst_is_device: 0 host, 1 device).
+ * xtraj[batch,N+1,13], utraj[batch,N,4], valid[batch] (uint8), qp_iters[batch] (int32, number of
+ * Riccati factorisations), sqp_iters[batch] (int32).  NULL pointers are skipped.  Synchronous. */
+int nmpc_get_trajectories(nmpc_handle_t *h, double *xtraj, double *utraj, uint8_t *valid,
+                          int32_t dst_is_device);
+int nmpc_get_stats(nmpc_handle_t *h, int32_t *qp_iters, int32_t *sqp_iters, int32_t dst_is_device);
+/* Overwrite the warm-start store (host pointers), e.g. to resume a Monte-Carlo run. */
+int nmpc_set_trajectories(nmpc_handle_t *h, const double *xtraj, const double *utraj,
+                          const uint8_t *valid);
+
+/* Test hooks on the linearisation stage: discretise (x[n,13],u[n,4]) -> xn[n,13], A[n,13,13],
+ * B[n,13,4] (row-major, device pointers), i.e. what acados' ERK + expl_vde_forw returns. */
+int nmpc_discretize_device(nmpc_handle_t *h, int32_t n, const double *x, const double *u,
+                           double *xn, double *A, double *B, void *stream);
+
+/* Introspection */
+int nmpc_batch(const nmpc_handle_t *h);
+int nmpc_horizon(const nmpc_handle_t *h);
+int64_t nmpc_workspace_bytes(const nmpc_handle_t *h);
+int nmpc_kernel_launches(const nmpc_handle_t *h); /* kernels launched so far by this handle */
+const char *nmpc_strerror(int code);
+const char *nmpc_last_error(void); /* text of the last CUDA error seen by this library */
+const char *nmpc_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NMPC_B200_H */

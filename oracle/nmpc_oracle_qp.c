@@ -331,6 +331,7 @@ int orc_qp_solve(const orc_qp *qp, int iter_max, double tol, double *dx, double 
     status = ORC_QP_FAILURE;
     goto done;
   }
+  it = 1; /* iterations are counted in Riccati factorisations */
   {
     int feasible = 1;
     for (int i = 0; i < nb; i++)
@@ -356,7 +357,6 @@ int orc_qp_solve(const orc_qp *qp, int iter_max, double tol, double *dx, double 
     res0 = fmax(res0, fmax(fabs(rbl0[i]), fabs(rbu0[i])));
     res0 = fmax(res0, fabs(ru0[i]));
   }
-  it = 1;
   double rho = 1.0;
 
   for (; it < iter_max; it++) {

@@ -1,0 +1,493 @@
+// nmpc_abi.cu -- kernels + C ABI of libnmpc_b200.so (see include/nmpc_b200.h).
+// Built for sm_100a only; there is no CPU fallback: without a CUDA device nmpc_create fails.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <new>
+
+#include "../../include/nmpc_b200.h"
+#include "nmpc_solver.cuh"
+
+using namespace nmpc;
+
+namespace {
+
+constexpr int WARPS = 4;  // warps (= problems in flight) per CTA; warps never synchronise
+
+constexpr int smem_elems_per_warp() { return (SmemLayout::total + 3) & ~3; }
+
+// ---------------------------------------------------------------- kernels
+template <typename T, int NS>
+__global__ void __launch_bounds__(WARPS * 32)
+    nmpc_solve_kernel(const __grid_constant__ SolveArgs<T> A, const __grid_constant__ WsLayout L,
+                      int* __restrict__ work_counter) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  T* sm = reinterpret_cast<T*>(smem_raw) + warp * smem_elems_per_warp();
+  const int slot = blockIdx.x * WARPS + warp;
+  T* ws = A.ws + (size_t)slot * L.total;
+  // dynamic work queue: iteration counts differ per problem, so problems are handed out one
+  // at a time instead of in a fixed stride
+  for (;;) {
+    int prob = 0;
+    if (lane == 0) prob = atomicAdd(work_counter, 1);
+    prob = __shfl_sync(FULL, prob, 0);
+    if (prob >= A.batch) break;
+    solve_one<T, NS>(A, L, ws, sm, prob, lane);
+  }
+}
+
+// Test hook: discretise n independent (x,u) pairs, one warp each.
+template <typename T, int NS>
+__global__ void __launch_bounds__(WARPS * 32)
+    nmpc_discretize_kernel(const __grid_constant__ DevCfg<T> c, int n, const double* __restrict__ x,
+                           const double* __restrict__ u, double* __restrict__ xn,
+                           double* __restrict__ Aout, double* __restrict__ Bout) {
+  const int lane = threadIdx.x & 31;
+  const int idx = blockIdx.x * WARPS + (threadIdx.x >> 5);
+  if (idx >= n) return;
+  T xs[NX], us[NU], s[NX], su[NU];
+#pragma unroll
+  for (int i = 0; i < NX; i++) {
+    xs[i] = (T)x[(size_t)idx * NX + i];
+    s[i] = (lane - NU == i) ? T(1) : T(0);
+  }
+#pragma unroll
+  for (int i = 0; i < NU; i++) {
+    us[i] = (T)u[(size_t)idx * NU + i];
+    su[i] = (lane == i) ? T(1) : T(0);
+  }
+  erk_column<T, NS>(c, xs, us, s, su);
+#pragma unroll
+  for (int i = 0; i < NX; i++) {
+    if (lane < NU) Bout[((size_t)idx * NX + i) * NU + lane] = (double)s[i];
+    else if (lane < NZ) Aout[((size_t)idx * NX + i) * NX + (lane - NU)] = (double)s[i];
+    if (lane == i) xn[(size_t)idx * NX + i] = (double)xs[i];
+  }
+}
+
+__global__ void fill_last_cmd_kernel(double* last, int n, double hover) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) last[i] = hover;
+}
+
+thread_local char g_err[512] = "";
+
+template <typename T>
+DevCfg<T> make_devcfg(const nmpc_config_t& c) {
+  DevCfg<T> d;
+  memset(&d, 0, sizeof(d));
+  d.N = c.N;
+  d.qp_iter_max = c.qp_iter_max;
+  d.integ_steps = c.integ_steps;
+  d.max_sqp_iter = c.max_sqp_iter;
+  d.nan_status = c.nan_status;
+  d.dt = (T)c.dt;
+  d.h = (T)(c.dt / (double)c.integ_steps);
+  const double sc = c.cost_scale_dt ? c.dt : 1.0;
+  const double lm_s = c.lm_scaled_by_dt ? c.lm * c.dt : c.lm;
+  for (int i = 0; i < NX; i++) {
+    d.Wq[i] = (T)(sc * c.W[i]);
+    d.Qd[i] = (T)(sc * c.W[i] + lm_s);
+    d.We[i] = (T)c.We[i];
+    d.QN[i] = (T)(c.We[i] + c.lm);
+  }
+  for (int i = 0; i < NU; i++) {
+    d.Wr[i] = (T)(sc * c.W[NX + i]);
+    d.Rd[i] = (T)(sc * c.W[NX + i] + lm_s);
+    d.rx[i] = (T)c.rotor_x[i];
+    d.ry[i] = (T)c.rotor_y[i];
+    d.rz[i] = (T)c.rotor_z[i];
+    d.lbu[i] = (T)c.lbu[i];
+    d.ubu[i] = (T)c.ubu[i];
+  }
+  d.inv_mass = (T)(1.0 / c.mass);
+  d.gravity = (T)c.gravity;
+  for (int i = 0; i < 3; i++) {
+    d.J[i] = (T)c.J[i];
+    d.invJ[i] = (T)(1.0 / c.J[i]);
+  }
+  d.kf = (T)c.kf;
+  d.w_min = (T)c.w_min;
+  d.w_max = (T)c.w_max;
+  d.hover = (T)(c.mass * c.gravity / 4.0);
+  d.sqp_tol = (T)c.sqp_tol;
+  double tol = c.ipm_tol;
+  if (sizeof(T) == 4 && tol < 1e-6) tol = 1e-6;  // FP32 cannot resolve a tighter complementarity
+  d.ipm_tol = (T)tol;
+  return d;
+}
+
+}  // namespace
+
+struct nmpc_handle {
+  nmpc_config_t cfg;
+  int batch, device, sm_count, grid, nslots, launches;
+  WsLayout L;
+  size_t ws_bytes;
+  void* ws;
+  double *xtraj, *utraj, *last_cmd;
+  uint8_t* valid;
+  int *qp_iters, *sqp_iters, *counter;
+  // staging for nmpc_solve_host
+  double *s_x0, *s_yref, *s_yref_e, *s_u0, *s_thrust, *s_speed;
+  int* s_status;
+  cudaStream_t stream;
+};
+
+#define CK(call)                                                                         \
+  do {                                                                                   \
+    cudaError_t e_ = (call);                                                             \
+    if (e_ != cudaSuccess) {                                                             \
+      snprintf(g_err, sizeof(g_err), "%s:%d %s: %s", __FILE__, __LINE__, #call,          \
+               cudaGetErrorString(e_));                                                  \
+      return (e_ == cudaErrorMemoryAllocation) ? NMPC_E_NOMEM : NMPC_E_CUDA;             \
+    }                                                                                    \
+  } while (0)
+
+static int validate(const nmpc_config_t* c) {
+  if (!c) return NMPC_E_INVALID;
+  if (c->N < 1 || c->N > 600) return NMPC_E_INVALID;
+  if (!(c->dt > 0.0)) return NMPC_E_INVALID;
+  if (c->integ_ns != 1 && c->integ_ns != 2 && c->integ_ns != 4) return NMPC_E_INVALID;
+  if (c->integ_steps < 1 || c->qp_iter_max < 1) return NMPC_E_INVALID;
+  if (c->precision != NMPC_PRECISION_F64 && c->precision != NMPC_PRECISION_F32)
+    return NMPC_E_INVALID;
+  if (!(c->mass > 0.0) || !(c->J[0] > 0.0) || !(c->J[1] > 0.0) || !(c->J[2] > 0.0))
+    return NMPC_E_INVALID;
+  for (int i = 0; i < 4; i++)
+    if (!(c->lbu[i] < c->ubu[i])) return NMPC_E_INVALID;
+  return NMPC_OK;
+}
+
+template <typename T, int NS>
+static int configure_kernel(nmpc_handle* h, size_t smem) {
+  auto kern = nmpc_solve_kernel<T, NS>;
+  CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int occ = 0;
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, WARPS * 32, smem));
+  if (occ < 1) occ = 1;
+  int grid = h->sm_count * occ;
+  const int need = (h->batch + WARPS - 1) / WARPS;
+  if (grid > need) grid = need;
+  h->grid = grid;
+  h->nslots = grid * WARPS;
+  return NMPC_OK;
+}
+
+template <typename T>
+static int configure_T(nmpc_handle* h) {
+  const size_t smem = (size_t)WARPS * smem_elems_per_warp() * sizeof(T);
+  switch (h->cfg.integ_ns) {
+    case 1: return configure_kernel<T, 1>(h, smem);
+    case 2: return configure_kernel<T, 2>(h, smem);
+    default: return configure_kernel<T, 4>(h, smem);
+  }
+}
+
+extern "C" {
+
+int nmpc_create(const nmpc_config_t* cfg, int32_t batch, int32_t device, nmpc_handle_t** out) {
+  if (!out) return NMPC_E_INVALID;
+  *out = nullptr;
+  int rc = validate(cfg);
+  if (rc != NMPC_OK || batch < 1) return NMPC_E_INVALID;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) {
+    snprintf(g_err, sizeof(g_err), "no CUDA device (libnmpc_b200 has no CPU fallback)");
+    return NMPC_E_NODEVICE;
+  }
+  if (device < 0 || device >= ndev) return NMPC_E_INVALID;
+  CK(cudaSetDevice(device));
+  nmpc_handle* h = new (std::nothrow) nmpc_handle();
+  if (!h) return NMPC_E_NOMEM;
+  memset(h, 0, sizeof(*h));
+  h->cfg = *cfg;
+  h->batch = batch;
+  h->device = device;
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, device));
+  h->sm_count = prop.multiProcessorCount;
+  h->L = make_layout(cfg->N);
+  rc = (cfg->precision == NMPC_PRECISION_F64) ? configure_T<double>(h) : configure_T<float>(h);
+  if (rc != NMPC_OK) {
+    delete h;
+    return rc;
+  }
+  const size_t esz = (cfg->precision == NMPC_PRECISION_F64) ? 8 : 4;
+  h->ws_bytes = (size_t)h->nslots * h->L.total * esz;
+  const size_t N = cfg->N, B = batch;
+  CK(cudaMalloc(&h->ws, h->ws_bytes));
+  CK(cudaMalloc(&h->xtraj, B * (N + 1) * NX * sizeof(double)));
+  CK(cudaMalloc(&h->utraj, B * N * NU * sizeof(double)));
+  CK(cudaMalloc(&h->last_cmd, B * NU * sizeof(double)));
+  CK(cudaMalloc(&h->valid, B));
+  CK(cudaMalloc(&h->qp_iters, B * sizeof(int)));
+  CK(cudaMalloc(&h->sqp_iters, B * sizeof(int)));
+  CK(cudaMalloc(&h->counter, sizeof(int)));
+  CK(cudaMalloc(&h->s_x0, B * NX * sizeof(double)));
+  CK(cudaMalloc(&h->s_yref, B * N * NZ * sizeof(double)));
+  CK(cudaMalloc(&h->s_yref_e, B * NX * sizeof(double)));
+  CK(cudaMalloc(&h->s_u0, B * NU * sizeof(double)));
+  CK(cudaMalloc(&h->s_thrust, B * NU * sizeof(double)));
+  CK(cudaMalloc(&h->s_speed, B * NU * sizeof(double)));
+  CK(cudaMalloc(&h->s_status, B * sizeof(int)));
+  CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+  CK(cudaMemset(h->ws, 0, h->ws_bytes));
+  CK(cudaMemset(h->xtraj, 0, B * (N + 1) * NX * sizeof(double)));
+  CK(cudaMemset(h->utraj, 0, B * N * NU * sizeof(double)));
+  CK(cudaMemset(h->valid, 0, B));
+  CK(cudaMemset(h->qp_iters, 0, B * sizeof(int)));
+  CK(cudaMemset(h->sqp_iters, 0, B * sizeof(int)));
+  *out = h;
+  return nmpc_reset_last_command(h);
+}
+
+int nmpc_destroy(nmpc_handle_t* h) {
+  if (!h) return NMPC_OK;
+  cudaSetDevice(h->device);
+  cudaFree(h->ws);
+  cudaFree(h->xtraj);
+  cudaFree(h->utraj);
+  cudaFree(h->last_cmd);
+  cudaFree(h->valid);
+  cudaFree(h->qp_iters);
+  cudaFree(h->sqp_iters);
+  cudaFree(h->counter);
+  cudaFree(h->s_x0);
+  cudaFree(h->s_yref);
+  cudaFree(h->s_yref_e);
+  cudaFree(h->s_u0);
+  cudaFree(h->s_thrust);
+  cudaFree(h->s_speed);
+  cudaFree(h->s_status);
+  if (h->stream) cudaStreamDestroy(h->stream);
+  delete h;
+  return NMPC_OK;
+}
+
+int nmpc_reset_last_command(nmpc_handle_t* h) {
+  if (!h) return NMPC_E_INVALID;
+  CK(cudaSetDevice(h->device));
+  const int n = h->batch * NU;
+  const double hover = h->cfg.mass * h->cfg.gravity / 4.0;  // mpc_controller_node:64
+  fill_last_cmd_kernel<<<(n + 255) / 256, 256>>>(h->last_cmd, n, hover);
+  h->launches++;
+  CK(cudaGetLastError());
+  CK(cudaDeviceSynchronize());
+  return NMPC_OK;
+}
+
+int nmpc_reconfigure(nmpc_handle_t* h, const nmpc_config_t* cfg) {
+  if (!h) return NMPC_E_INVALID;
+  int rc = validate(cfg);
+  if (rc != NMPC_OK) return rc;
+  if (cfg->N != h->cfg.N || cfg->precision != h->cfg.precision) return NMPC_E_INVALID;
+  CK(cudaSetDevice(h->device));
+  CK(cudaDeviceSynchronize());
+  const int old_ns = h->cfg.integ_ns;
+  h->cfg = *cfg;
+  if (cfg->integ_ns != old_ns) {
+    const int slots = h->nslots;
+    rc = (cfg->precision == NMPC_PRECISION_F64) ? configure_T<double>(h) : configure_T<float>(h);
+    if (rc != NMPC_OK) return rc;
+    if (h->nslots > slots) {  // never exceed the allocated workspace
+      h->nslots = slots;
+      h->grid = slots / WARPS;
+    }
+  }
+  CK(cudaMemset(h->valid, 0, h->batch));  // controller.py:167
+  return NMPC_OK;
+}
+
+int nmpc_set_bounds(nmpc_handle_t* h, const double lbu[4], const double ubu[4]) {
+  if (!h || !lbu || !ubu) return NMPC_E_INVALID;
+  for (int i = 0; i < 4; i++)
+    if (!(lbu[i] < ubu[i])) return NMPC_E_INVALID;
+  for (int i = 0; i < 4; i++) {
+    h->cfg.lbu[i] = lbu[i];
+    h->cfg.ubu[i] = ubu[i];
+  }
+  return NMPC_OK;
+}
+
+int nmpc_invalidate(nmpc_handle_t* h, const uint8_t* mask) {
+  if (!h) return NMPC_E_INVALID;
+  CK(cudaSetDevice(h->device));
+  CK(cudaDeviceSynchronize());
+  if (!mask) {
+    CK(cudaMemset(h->valid, 0, h->batch));
+    return NMPC_OK;
+  }
+  uint8_t* tmp = new (std::nothrow) uint8_t[h->batch];
+  if (!tmp) return NMPC_E_NOMEM;
+  cudaError_t e = cudaMemcpy(tmp, h->valid, h->batch, cudaMemcpyDeviceToHost);
+  if (e == cudaSuccess) {
+    for (int i = 0; i < h->batch; i++)
+      if (mask[i]) tmp[i] = 0;
+    e = cudaMemcpy(h->valid, tmp, h->batch, cudaMemcpyHostToDevice);
+  }
+  delete[] tmp;
+  CK(e);
+  return NMPC_OK;
+}
+
+extern "C++" {
+template <typename T, int NS>
+static int launch_solve(nmpc_handle* h, const double* x0, const double* yref, const double* yref_e,
+                        double* u0, int32_t* status, double* thrust, double* speed,
+                        cudaStream_t st) {
+  SolveArgs<T> A;
+  A.cfg = make_devcfg<T>(h->cfg);
+  A.batch = h->batch;
+  A.x0 = x0;
+  A.yref = yref;
+  A.yref_e = yref_e;
+  A.xtraj = h->xtraj;
+  A.utraj = h->utraj;
+  A.valid = h->valid;
+  A.last_cmd = h->last_cmd;
+  A.u0 = u0;
+  A.status = status;
+  A.thrust = thrust;
+  A.speed = speed;
+  A.qp_iters = h->qp_iters;
+  A.sqp_iters = h->sqp_iters;
+  A.ws = reinterpret_cast<T*>(h->ws);
+  const size_t smem = (size_t)WARPS * smem_elems_per_warp() * sizeof(T);
+  CK(cudaMemsetAsync(h->counter, 0, sizeof(int), st));
+  nmpc_solve_kernel<T, NS><<<h->grid, WARPS * 32, smem, st>>>(A, h->L, h->counter);
+  h->launches++;
+  CK(cudaGetLastError());
+  return NMPC_OK;
+}
+
+template <typename T>
+static int launch_solve_T(nmpc_handle* h, const double* x0, const double* yref,
+                          const double* yref_e, double* u0, int32_t* status, double* thrust,
+                          double* speed, cudaStream_t st) {
+  switch (h->cfg.integ_ns) {
+    case 1: return launch_solve<T, 1>(h, x0, yref, yref_e, u0, status, thrust, speed, st);
+    case 2: return launch_solve<T, 2>(h, x0, yref, yref_e, u0, status, thrust, speed, st);
+    default: return launch_solve<T, 4>(h, x0, yref, yref_e, u0, status, thrust, speed, st);
+  }
+}
+}  // extern "C++"
+
+int nmpc_solve_device(nmpc_handle_t* h, const double* x0, const double* yref, const double* yref_e,
+                      double* u0, int32_t* status, double* thrust, double* speed, void* stream) {
+  if (!h || !x0 || !yref || !yref_e) return NMPC_E_INVALID;
+  CK(cudaSetDevice(h->device));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (h->cfg.precision == NMPC_PRECISION_F64)
+    return launch_solve_T<double>(h, x0, yref, yref_e, u0, status, thrust, speed, st);
+  return launch_solve_T<float>(h, x0, yref, yref_e, u0, status, thrust, speed, st);
+}
+
+int nmpc_solve_host(nmpc_handle_t* h, const double* x0, const double* yref, const double* yref_e,
+                    double* u0, int32_t* status, double* thrust, double* speed) {
+  if (!h || !x0 || !yref || !yref_e) return NMPC_E_INVALID;
+  CK(cudaSetDevice(h->device));
+  const size_t B = h->batch, N = h->cfg.N;
+  cudaStream_t st = h->stream;
+  CK(cudaMemcpyAsync(h->s_x0, x0, B * NX * sizeof(double), cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(h->s_yref, yref, B * N * NZ * sizeof(double), cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(h->s_yref_e, yref_e, B * NX * sizeof(double), cudaMemcpyHostToDevice, st));
+  int rc = nmpc_solve_device(h, h->s_x0, h->s_yref, h->s_yref_e, h->s_u0, h->s_status, h->s_thrust,
+                             h->s_speed, st);
+  if (rc != NMPC_OK) return rc;
+  if (u0) CK(cudaMemcpyAsync(u0, h->s_u0, B * NU * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (status) CK(cudaMemcpyAsync(status, h->s_status, B * sizeof(int), cudaMemcpyDeviceToHost, st));
+  if (thrust)
+    CK(cudaMemcpyAsync(thrust, h->s_thrust, B * NU * sizeof(double), cudaMemcpyDeviceToHost, st));
+  if (speed)
+    CK(cudaMemcpyAsync(speed, h->s_speed, B * NU * sizeof(double), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return NMPC_OK;
+}
+
+int nmpc_get_trajectories(nmpc_handle_t* h, double* xtraj, double* utraj, uint8_t* valid,
+                          int32_t dst_is_device) {
+  if (!h) return NMPC_E_INVALID;
+  CK(cudaSetDevice(h->device));
+  CK(cudaDeviceSynchronize());
+  const size_t B = h->batch, N = h->cfg.N;
+  const cudaMemcpyKind kind = dst_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+  if (xtraj) CK(cudaMemcpy(xtraj, h->xtraj, B * (N + 1) * NX * sizeof(double), kind));
+  if (utraj) CK(cudaMemcpy(utraj, h->utraj, B * N * NU * sizeof(double), kind));
+  if (valid) CK(cudaMemcpy(valid, h->valid, B, kind));
+  return NMPC_OK;
+}
+
+int nmpc_set_trajectories(nmpc_handle_t* h, const double* xtraj, const double* utraj,
+                          const uint8_t* valid) {
+  if (!h) return NMPC_E_INVALID;
+  CK(cudaSetDevice(h->device));
+  CK(cudaDeviceSynchronize());
+  const size_t B = h->batch, N = h->cfg.N;
+  if (xtraj)
+    CK(cudaMemcpy(h->xtraj, xtraj, B * (N + 1) * NX * sizeof(double), cudaMemcpyHostToDevice));
+  if (utraj) CK(cudaMemcpy(h->utraj, utraj, B * N * NU * sizeof(double), cudaMemcpyHostToDevice));
+  if (valid) CK(cudaMemcpy(h->valid, valid, B, cudaMemcpyHostToDevice));
+  return NMPC_OK;
+}
+
+int nmpc_get_stats(nmpc_handle_t* h, int32_t* qp_iters, int32_t* sqp_iters,
+                   int32_t dst_is_device) {
+  if (!h) return NMPC_E_INVALID;
+  CK(cudaSetDevice(h->device));
+  CK(cudaDeviceSynchronize());
+  const size_t B = h->batch;
+  const cudaMemcpyKind kind = dst_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+  if (qp_iters) CK(cudaMemcpy(qp_iters, h->qp_iters, B * sizeof(int), kind));
+  if (sqp_iters) CK(cudaMemcpy(sqp_iters, h->sqp_iters, B * sizeof(int), kind));
+  return NMPC_OK;
+}
+
+extern "C++" {
+template <typename T>
+static int launch_disc(nmpc_handle* h, int n, const double* x, const double* u, double* xn,
+                       double* A, double* B, cudaStream_t st) {
+  DevCfg<T> c = make_devcfg<T>(h->cfg);
+  const int grid = (n + WARPS - 1) / WARPS;
+  switch (h->cfg.integ_ns) {
+    case 1: nmpc_discretize_kernel<T, 1><<<grid, WARPS * 32, 0, st>>>(c, n, x, u, xn, A, B); break;
+    case 2: nmpc_discretize_kernel<T, 2><<<grid, WARPS * 32, 0, st>>>(c, n, x, u, xn, A, B); break;
+    default: nmpc_discretize_kernel<T, 4><<<grid, WARPS * 32, 0, st>>>(c, n, x, u, xn, A, B); break;
+  }
+  h->launches++;
+  CK(cudaGetLastError());
+  return NMPC_OK;
+}
+}  // extern "C++"
+
+int nmpc_discretize_device(nmpc_handle_t* h, int32_t n, const double* x, const double* u,
+                           double* xn, double* A, double* B, void* stream) {
+  if (!h || n < 1 || !x || !u || !xn || !A || !B) return NMPC_E_INVALID;
+  CK(cudaSetDevice(h->device));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (h->cfg.precision == NMPC_PRECISION_F64) return launch_disc<double>(h, n, x, u, xn, A, B, st);
+  return launch_disc<float>(h, n, x, u, xn, A, B, st);
+}
+
+int nmpc_batch(const nmpc_handle_t* h) { return h ? h->batch : NMPC_E_INVALID; }
+int nmpc_horizon(const nmpc_handle_t* h) { return h ? h->cfg.N : NMPC_E_INVALID; }
+int64_t nmpc_workspace_bytes(const nmpc_handle_t* h) { return h ? (int64_t)h->ws_bytes : -1; }
+int nmpc_kernel_launches(const nmpc_handle_t* h) { return h ? h->launches : NMPC_E_INVALID; }
+
+const char* nmpc_strerror(int code) {
+  switch (code) {
+    case NMPC_OK: return "ok";
+    case NMPC_E_INVALID: return "invalid argument or unsupported configuration";
+    case NMPC_E_CUDA: return "CUDA runtime error";
+    case NMPC_E_NOMEM: return "out of memory";
+    case NMPC_E_NODEVICE: return "no CUDA device (no CPU fallback exists)";
+    default: return "unknown error";
+  }
+}
+const char* nmpc_last_error(void) { return g_err; }
+const char* nmpc_version(void) { return "nmpc_b200 0.1 (sm_100a)"; }
+
+}  // extern "C"

@@ -1,0 +1,756 @@
+// nmpc_solver.cuh -- one-warp-per-problem SQP / Riccati interior-point solver, sm_100a.
+//
+// Replaces, for the OCP of /root/reference/src/rotors_mpc_controller/controller.py:175-264,
+// what `solver.solve()` (controller.py:447) runs inside acados: ERK + forward sensitivities,
+// LINEAR_LS Gauss-Newton assembly + Levenberg-Marquardt, the HPIPM QP solve and the full
+// step.  Nothing here is derived from acados / HPIPM sources (they are not in the reference
+// tree); the algorithm is the textbook stage-wise Riccati recursion inside a Mehrotra
+// predictor-corrector, laid out for one warp:
+//
+//   lane j (0..16) owns COLUMN j of the stage matrix M_k = [B_k | A_k] (13 x 17) and of every
+//   matrix derived from it (W = P M, G = M' W), kept in registers; the 13x13 cost-to-go P,
+//   the staged M_k and the feedback K_k are broadcast through a 4 KB per-warp shared-memory
+//   tile; 4x4 input blocks are exchanged with warp shuffles and factorised redundantly.
+//   Per-stage factors (K, Quu^-1, k) and all horizon-long vectors live in an L2-resident
+//   global workspace slot owned by the warp (sized by N, so N = 600 runs unchanged).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "nmpc_model.cuh"
+
+namespace nmpc {
+
+constexpr unsigned FULL = 0xffffffffu;
+
+enum : int { ST_SUCCESS = 0, ST_NAN = 1, ST_MAXITER = 2, ST_MINSTEP = 3, ST_QPFAIL = 4 };
+
+// Offsets (in elements of T) inside one workspace slot.
+struct WsLayout {
+  int N;
+  size_t M, K, Qi, kff, kffd;
+  size_t xb, q, b, dx, xa;                                            // x-type vectors
+  size_t ub, r, lb, ubd, du, ua, tl, tu, ll, lu, rbl0, rbu0, ru0;    // u-type vectors
+  size_t dtl, dtu, dll, dlu, Rt, rt, dr;
+  size_t total;
+};
+
+__host__ __device__ inline WsLayout make_layout(int N) {
+  WsLayout L;
+  L.N = N;
+  size_t o = 0;
+  auto take = [&](size_t n) {
+    size_t r = o;
+    o += (n + 3) & ~size_t(3);  // keep 32-byte alignment for T = double
+    return r;
+  };
+  const size_t nx = (size_t)(N + 1) * NX, nu = (size_t)N * NU;
+  L.M = take((size_t)N * NX * NZ);
+  L.K = take((size_t)N * NU * NX);
+  L.Qi = take((size_t)N * 16);
+  L.kff = take(nu);
+  L.kffd = take(nu);
+  L.xb = take(nx);
+  L.q = take(nx);
+  L.b = take(nx);
+  L.dx = take(nx);
+  L.xa = take(nx);
+  L.ub = take(nu);
+  L.r = take(nu);
+  L.lb = take(nu);
+  L.ubd = take(nu);
+  L.du = take(nu);
+  L.ua = take(nu);
+  L.tl = take(nu);
+  L.tu = take(nu);
+  L.ll = take(nu);
+  L.lu = take(nu);
+  L.rbl0 = take(nu);
+  L.rbu0 = take(nu);
+  L.ru0 = take(nu);
+  L.dtl = take(nu);
+  L.dtu = take(nu);
+  L.dll = take(nu);
+  L.dlu = take(nu);
+  L.Rt = take(nu);
+  L.rt = take(nu);
+  L.dr = take(nu);
+  L.total = o;
+  return L;
+}
+
+// Per-warp shared-memory tile (elements of T).
+constexpr int SP_LD = 14;  // padded leading dimension of P and K rows (16-byte aligned rows)
+constexpr int SM_LD = 18;  // padded leading dimension of the staged M rows
+struct SmemLayout {
+  static constexpr int P = 0;                    // 13 x 14
+  static constexpr int M = P + NX * SP_LD;       // 13 x 18
+  static constexpr int K = M + NX * SM_LD;       // 4 x 14
+  static constexpr int p = K + NU * SP_LD;       // 13 (+1)
+  static constexpr int wv = p + 14;              // 13 (+1)
+  static constexpr int xA = wv + 14;             // 13 (+1) forward-sweep state, ping
+  static constexpr int xB = xA + 14;             // pong
+  static constexpr int u = xB + 14;              // 4
+  static constexpr int total = u + 4;            // 548 elements
+};
+
+template <typename T>
+__device__ __forceinline__ T warp_sum(T v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+  return v;
+}
+template <typename T>
+__device__ __forceinline__ T warp_min(T v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(FULL, v, o));
+  return v;
+}
+template <typename T>
+__device__ __forceinline__ T warp_max(T v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(FULL, v, o));
+  return v;
+}
+template <typename T>
+__device__ __forceinline__ bool finite_(T v) {
+  return (v - v) == T(0);
+}
+
+// Inverse of a symmetric positive definite 4x4 (lower triangle of G used) via Cholesky.
+// Executed redundantly by every lane.  Returns false on a non-positive / NaN pivot.
+template <typename T>
+__device__ __forceinline__ bool spd4_inverse(const T (&G)[4][4], T (&Gi)[4][4]) {
+  T L[4][4], Li[4][4];
+  bool ok = true;
+#pragma unroll
+  for (int j = 0; j < 4; j++) {
+    T d = G[j][j];
+#pragma unroll
+    for (int k = 0; k < j; k++) d -= L[j][k] * L[j][k];
+    ok = ok && (d > T(0));
+    const T ljj = sqrt(d);
+    const T inv = T(1) / ljj;
+    L[j][j] = ljj;
+    Li[j][j] = inv;
+#pragma unroll
+    for (int i = j + 1; i < 4; i++) {
+      T s = G[i][j];
+#pragma unroll
+      for (int k = 0; k < j; k++) s -= L[i][k] * L[j][k];
+      L[i][j] = s * inv;
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 4; j++) {
+#pragma unroll
+    for (int i = j + 1; i < 4; i++) {
+      T s = T(0);
+#pragma unroll
+      for (int k = j; k < i; k++) s -= L[i][k] * Li[k][j];
+      Li[i][j] = s * Li[i][i];
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+#pragma unroll
+    for (int j = 0; j <= i; j++) {
+      T s = T(0);
+#pragma unroll
+      for (int k = i; k < 4; k++) s += Li[k][i] * Li[k][j];
+      Gi[i][j] = s;
+      Gi[j][i] = s;
+    }
+  }
+  return ok;
+}
+
+// ------------------------------------------------------------------ K1: linearisation
+// For every stage: ERK + forward sensitivities -> M_k = [B_k | A_k] (row-major 13 x 17 in the
+// workspace, so that lane j reads/writes column j coalesced) and the defect b_k.
+template <typename T, int NS>
+__device__ __forceinline__ void linearize(const DevCfg<T>& c, T* __restrict__ ws,
+                                          const WsLayout& L, int lane) {
+  const T* xb = ws + L.xb;
+  const T* ub = ws + L.ub;
+  T* M = ws + L.M;
+  T* bv = ws + L.b;
+  for (int k = 0; k < c.N; k++) {
+    T x[NX], u[NU], s[NX], su[NU];
+#pragma unroll
+    for (int i = 0; i < NX; i++) {
+      x[i] = xb[k * NX + i];
+      s[i] = (lane - NU == i) ? T(1) : T(0);
+    }
+#pragma unroll
+    for (int i = 0; i < NU; i++) {
+      u[i] = ub[k * NU + i];
+      su[i] = (lane == i) ? T(1) : T(0);
+    }
+    erk_column<T, NS>(c, x, u, s, su);
+    if (lane < NZ) {
+#pragma unroll
+      for (int i = 0; i < NX; i++) M[((size_t)k * NX + i) * NZ + lane] = s[i];
+    }
+#pragma unroll
+    for (int i = 0; i < NX; i++)
+      if (lane == i) bv[k * NX + i] = x[i] - xb[(k + 1) * NX + i];
+  }
+}
+
+// LINEAR_LS gradients (controller.py:223-245, stage cost scaled by dt) and the delta-form box.
+template <typename T>
+__device__ __forceinline__ void gradients(const DevCfg<T>& c, T* __restrict__ ws,
+                                          const WsLayout& L, const double* __restrict__ yref,
+                                          const double* __restrict__ yref_e, int lane) {
+  const int N = c.N;
+  const T* xb = ws + L.xb;
+  const T* ub = ws + L.ub;
+  for (int idx = lane; idx < N * NX; idx += 32) {
+    const int k = idx / NX, i = idx - k * NX;
+    ws[L.q + idx] = c.Wq[i] * (xb[idx] - (T)yref[(size_t)k * NZ + i]);
+  }
+  if (lane < NX) ws[L.q + N * NX + lane] = c.We[lane] * (xb[N * NX + lane] - (T)yref_e[lane]);
+  for (int idx = lane; idx < N * NU; idx += 32) {
+    const int k = idx >> 2, a = idx & 3;
+    const T u = ub[idx];
+    ws[L.r + idx] = c.Wr[a] * (u - (T)yref[(size_t)k * NZ + NX + a]);
+    ws[L.lb + idx] = c.lbu[a] - u;
+    ws[L.ubd + idx] = c.ubu[a] - u;
+    ws[L.Rt + idx] = c.Rd[a];
+  }
+}
+
+// ------------------------------------------------------------------ K2: Riccati factorisation
+// Backward sweep with input Hessian diagonal Rt and input gradient rt (both N x 4 in the
+// workspace), fused with the right-hand side (rho*b, rho*q, rt); rho is 1 for the
+// equality-constrained phase-0 solve and 0 afterwards (see ipm_solve).  Writes K_k, Quu_k^-1
+// and the feed-forward k_k per stage.  Returns false on a non-positive pivot / NaN.
+template <typename T>
+__device__ __forceinline__ bool factor_sweep(const DevCfg<T>& c, T* __restrict__ ws,
+                                             const WsLayout& L, T* __restrict__ sm, int lane,
+                                             bool rho1) {
+  const int N = c.N;
+  T* sP = sm + SmemLayout::P;
+  T* sM = sm + SmemLayout::M;
+  T* sK = sm + SmemLayout::K;
+  T* sp = sm + SmemLayout::p;
+  T* swv = rho1 ? (sm + SmemLayout::wv) : sp;
+  const int jx = lane - NU;                 // state index owned by an x-lane
+  const bool xlane = (lane >= NU) && (lane < NZ);
+  const bool active = lane < NZ;
+  bool ok = true;
+
+  // terminal cost-to-go: P = diag(QN), p = rho * q_N
+  if (xlane) {
+#pragma unroll
+    for (int i = 0; i < NX; i++) sP[jx * SP_LD + i] = (i == jx) ? c.QN[jx] : T(0);
+    sp[jx] = rho1 ? ws[L.q + (size_t)N * NX + jx] : T(0);
+  }
+  __syncwarp();
+
+  for (int k = N - 1; k >= 0; k--) {
+    const T* Mk = ws + L.M + (size_t)k * NX * NZ;
+    // 1. this lane's column of M_k (coalesced row-major reads), staged to shared memory
+    T m[NX];
+    if (active) {
+#pragma unroll
+      for (int i = 0; i < NX; i++) {
+        m[i] = Mk[i * NZ + lane];
+        sM[i * SM_LD + lane] = m[i];
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < NX; i++) m[i] = T(0);
+    }
+    if (rho1 && xlane) {  // wv = P b_k + p
+      T s = sp[jx];
+#pragma unroll
+      for (int cc = 0; cc < NX; cc++) s += sP[jx * SP_LD + cc] * ws[L.b + (size_t)k * NX + cc];
+      swv[jx] = s;
+    }
+    // 2. w = P m   (P broadcast from shared memory)
+    T w[NX];
+#pragma unroll
+    for (int i = 0; i < NX; i++) {
+      T s = T(0);
+#pragma unroll
+      for (int cc = 0; cc < NX; cc++) s += sP[i * SP_LD + cc] * m[cc];
+      w[i] = s;
+    }
+    __syncwarp();
+    // 3. G(:,j) = M' w  and  g_j = m . wv + gradient_j
+    T G[NZ];
+#pragma unroll
+    for (int i = 0; i < NZ; i++) G[i] = T(0);
+#pragma unroll
+    for (int r = 0; r < NX; r++) {
+#pragma unroll
+      for (int i = 0; i < NZ; i++) G[i] += sM[r * SM_LD + i] * w[r];
+    }
+    T g = T(0);
+#pragma unroll
+    for (int r = 0; r < NX; r++) g += m[r] * swv[r];
+    if (lane < NU) {
+      g += ws[L.rt + (size_t)k * NU + lane];
+    } else if (xlane && rho1) {
+      g += ws[L.q + (size_t)k * NX + jx];
+    }
+    {
+      T d = T(0);
+      if (lane < NU) d = ws[L.Rt + (size_t)k * NU + lane];
+      else if (xlane) d = c.Qd[jx];
+#pragma unroll
+      for (int i = 0; i < NZ; i++)
+        if (i == lane) G[i] += d;
+    }
+    // 4. Quu (lanes 0..3 hold its columns) -> every lane; inverse computed redundantly
+    T Quu[4][4], Qi[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+      for (int a = 0; a <= i; a++) {
+        Quu[i][a] = __shfl_sync(FULL, G[i], a);
+        Quu[a][i] = Quu[i][a];
+      }
+    ok = spd4_inverse(Quu, Qi) && ok;
+    T gu[4], kf[4];
+#pragma unroll
+    for (int a = 0; a < 4; a++) gu[a] = __shfl_sync(FULL, g, a);
+#pragma unroll
+    for (int a = 0; a < 4; a++) {
+      T s = T(0);
+#pragma unroll
+      for (int l = 0; l < 4; l++) s -= Qi[a][l] * gu[l];
+      kf[a] = s;
+    }
+    // 5. feedback column K(:,jx) = -Quu^-1 Qux(:,jx)
+    if (xlane) {
+#pragma unroll
+      for (int a = 0; a < 4; a++) {
+        T s = T(0);
+#pragma unroll
+        for (int l = 0; l < 4; l++) s -= Qi[a][l] * G[l];
+        sK[a * SP_LD + jx] = s;
+        ws[L.K + ((size_t)k * NU + a) * NX + jx] = s;
+      }
+    }
+    if (lane < NU) {
+#pragma unroll
+      for (int a = 0; a < 4; a++)
+        if (a == lane) {
+          ws[L.kff + (size_t)k * NU + a] = kf[a];
+#pragma unroll
+          for (int l = 0; l < 4; l++) ws[L.Qi + (size_t)k * 16 + a * 4 + l] = Qi[a][l];
+        }
+    }
+    __syncwarp();
+    // 6. cost-to-go row jx:  P(jx,:) = Qxx(jx,:) + Qux(:,jx)' K ,  p_jx = g + Qux(:,jx)' k
+    if (xlane && k > 0) {
+      T pn = g;
+#pragma unroll
+      for (int a = 0; a < 4; a++) pn += G[a] * kf[a];
+#pragma unroll
+      for (int i = 0; i < NX; i++) {
+        T s = G[NU + i];
+#pragma unroll
+        for (int a = 0; a < 4; a++) s += G[a] * sK[a * SP_LD + i];
+        sP[jx * SP_LD + i] = s;
+      }
+      sp[jx] = pn;
+    }
+    __syncwarp();
+  }
+  return ok;
+}
+
+// Forward roll-out  u_k = K_k x_k + kf_k,  x_{k+1} = A_k x_k + B_k u_k + rho b_k  from x_0 = 0.
+// kf points at kff (factor sweep) or kffd (delta sweep).  ACC: add into outX/outU.
+template <typename T, bool ACC>
+__device__ __forceinline__ void forward_sweep(const DevCfg<T>& c, T* __restrict__ ws,
+                                              const WsLayout& L, T* __restrict__ sm, int lane,
+                                              bool rho1, size_t kf_off, size_t outX, size_t outU) {
+  const int N = c.N;
+  T* sxa = sm + SmemLayout::xA;
+  T* sxb = sm + SmemLayout::xB;
+  T* su = sm + SmemLayout::u;
+  if (lane < NX) {
+    sxa[lane] = T(0);
+    if (!ACC) ws[outX + lane] = T(0);
+  }
+  __syncwarp();
+  for (int k = 0; k < N; k++) {
+    T* xin = (k & 1) ? sxb : sxa;
+    T* xout = (k & 1) ? sxa : sxb;
+    if (lane < NU) {
+      const T* Kr = ws + L.K + ((size_t)k * NU + lane) * NX;
+      T s = ws[kf_off + (size_t)k * NU + lane];
+#pragma unroll
+      for (int j = 0; j < NX; j++) s += Kr[j] * xin[j];
+      su[lane] = s;
+      if (ACC) ws[outU + (size_t)k * NU + lane] += s;
+      else ws[outU + (size_t)k * NU + lane] = s;
+    }
+    __syncwarp();
+    if (lane < NX) {
+      const T* Mr = ws + L.M + ((size_t)k * NX + lane) * NZ;
+      T s = rho1 ? ws[L.b + (size_t)k * NX + lane] : T(0);
+#pragma unroll
+      for (int a = 0; a < NU; a++) s += Mr[a] * su[a];
+#pragma unroll
+      for (int j = 0; j < NX; j++) s += Mr[NU + j] * xin[j];
+      xout[lane] = s;
+      if (ACC) ws[outX + (size_t)(k + 1) * NX + lane] += s;
+      else ws[outX + (size_t)(k + 1) * NX + lane] = s;
+    }
+    __syncwarp();
+  }
+}
+
+// Backward sweep for a right-hand side that differs only in the input gradient (b = 0, q = 0,
+// r = dr): reuses K_k and Quu_k^-1, writes the feed-forward kffd_k.
+template <typename T>
+__device__ __forceinline__ void delta_backward(const DevCfg<T>& c, T* __restrict__ ws,
+                                               const WsLayout& L, T* __restrict__ sm, int lane) {
+  const int N = c.N;
+  T* sp = sm + SmemLayout::p;
+  const int jx = lane - NU;
+  const bool xlane = (lane >= NU) && (lane < NZ);
+  if (lane < NX) sp[lane] = T(0);
+  __syncwarp();
+  for (int k = N - 1; k >= 0; k--) {
+    const T* Mk = ws + L.M + (size_t)k * NX * NZ;
+    T gz = T(0);
+    if (lane < NZ) {
+#pragma unroll
+      for (int r = 0; r < NX; r++) gz += Mk[r * NZ + lane] * sp[r];
+      if (lane < NU) gz += ws[L.dr + (size_t)k * NU + lane];
+    }
+    T gu[4];
+#pragma unroll
+    for (int a = 0; a < 4; a++) gu[a] = __shfl_sync(FULL, gz, a);
+    if (lane < NU) {
+      const T* Qr = ws + L.Qi + (size_t)k * 16 + lane * 4;
+      T s = T(0);
+#pragma unroll
+      for (int l = 0; l < 4; l++) s -= Qr[l] * gu[l];
+      ws[L.kffd + (size_t)k * NU + lane] = s;
+    }
+    T pn = gz;
+    if (xlane) {
+#pragma unroll
+      for (int a = 0; a < 4; a++) pn += ws[L.K + ((size_t)k * NU + a) * NX + jx] * gu[a];
+    }
+    __syncwarp();
+    if (xlane) sp[jx] = pn;
+    __syncwarp();
+  }
+}
+
+// ------------------------------------------------------------------ K2: interior point
+// Mehrotra predictor-corrector for   min 1/2 z'Hz + g'z  s.t. dynamics, lb <= du <= ub.
+//  phase 0: equality-constrained solve; if it respects the box it is the optimum (strictly
+//           convex QP) -> 1 factorisation, no interior-point iteration.
+//  else:    start there (dynamics and x-stationarity hold exactly), slacks t = max(slack, thr0),
+//           lam = mu0/t.  One step length for primal and dual, so the remaining linear residuals
+//           (box, u-stationarity) are rho = prod(1-alpha) times their initial values rbl0, rbu0,
+//           ru0 and every Newton right-hand side is built from those (no cancellation).
+// Returns the QP status; *iters = number of Riccati factorisations.
+template <typename T>
+__device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
+                                         const WsLayout& L, T* __restrict__ sm, int lane,
+                                         int* iters) {
+  const int N = c.N;
+  const int nb = N * NU;
+  const int nxv = (N + 1) * NX;
+  const T thr0 = T(0.1), mu0 = T(0.1);
+  int it = 0;
+
+  // finite check of the QP data (NaN state / reference -> QP failure, status 4)
+  {
+    bool fin = true;
+    for (int i = lane; i < nb; i += 32) {
+      fin = fin && finite_(ws[L.r + i]) && finite_(ws[L.lb + i]) && finite_(ws[L.ubd + i]);
+      ws[L.rt + i] = ws[L.r + i];
+    }
+    for (int i = lane; i < nxv; i += 32) fin = fin && finite_(ws[L.q + i]);
+    for (int i = lane; i < N * NX; i += 32) fin = fin && finite_(ws[L.b + i]);
+    if (!__all_sync(FULL, fin)) {
+      *iters = 0;
+      return ST_QPFAIL;
+    }
+  }
+  __syncwarp();
+  bool ok = factor_sweep(c, ws, L, sm, lane, true);
+  it = 1;
+  if (!ok) {
+    *iters = it;
+    return ST_QPFAIL;
+  }
+  forward_sweep<T, false>(c, ws, L, sm, lane, true, L.kff, L.dx, L.du);
+  // box check + interior-point start
+  bool feas = true;
+  T res0 = T(0);
+  for (int i = lane; i < nb; i += 32) {
+    const T du = ws[L.du + i], lb = ws[L.lb + i], ub = ws[L.ubd + i];
+    feas = feas && (du >= lb) && (du <= ub);
+    const T tl = fmax(du - lb, thr0), tu = fmax(ub - du, thr0);
+    const T ll = mu0 / tl, lu = mu0 / tu;
+    const T rbl = du - lb - tl, rbu = ub - du - tu, ru = -ll + lu;
+    ws[L.tl + i] = tl;
+    ws[L.tu + i] = tu;
+    ws[L.ll + i] = ll;
+    ws[L.lu + i] = lu;
+    ws[L.rbl0 + i] = rbl;
+    ws[L.rbu0 + i] = rbu;
+    ws[L.ru0 + i] = ru;
+    res0 = fmax(res0, fmax(fmax(fabs(rbl), fabs(rbu)), fabs(ru)));
+  }
+  if (__all_sync(FULL, feas)) {
+    *iters = it;
+    return ST_SUCCESS;
+  }
+  res0 = warp_max(res0);
+  T rho = T(1);
+  int status = ST_MAXITER;
+  const T inv2nb = T(1) / T(2 * nb);
+
+  for (; it < c.qp_iter_max; it++) {
+    // complementarity measure + predictor Hessian / gradient
+    T mu = T(0);
+    for (int i = lane; i < nb; i += 32) {
+      const T tl = ws[L.tl + i], tu = ws[L.tu + i], ll = ws[L.ll + i], lu = ws[L.lu + i];
+      mu += tl * ll + tu * lu;
+      const T dl = ll / tl, dw = lu / tu;
+      ws[L.Rt + i] = c.Rd[i & 3] + dl + dw;
+      ws[L.rt + i] = rho * ws[L.ru0 + i] + dl * (rho * ws[L.rbl0 + i]) + ll -
+                     dw * (rho * ws[L.rbu0 + i]) - lu;
+    }
+    mu = warp_sum(mu) * inv2nb;
+    if (!(mu == mu)) {
+      status = ST_QPFAIL;
+      break;
+    }
+    if (mu <= c.ipm_tol && rho * res0 <= c.ipm_tol) {
+      status = ST_SUCCESS;
+      break;
+    }
+    __syncwarp();
+    ok = factor_sweep(c, ws, L, sm, lane, false);
+    if (!ok) {
+      status = ST_QPFAIL;
+      break;
+    }
+    forward_sweep<T, false>(c, ws, L, sm, lane, false, L.kff, L.xa, L.ua);
+    // affine step length and centering parameter
+    T a_aff = T(1);
+    for (int i = lane; i < nb; i += 32) {
+      const T tl = ws[L.tl + i], tu = ws[L.tu + i], ll = ws[L.ll + i], lu = ws[L.lu + i];
+      const T ua = ws[L.ua + i];
+      const T dtl = ua + rho * ws[L.rbl0 + i];
+      const T dtu = -ua + rho * ws[L.rbu0 + i];
+      const T dll = -(ll / tl) * dtl - ll;
+      const T dlu = -(lu / tu) * dtu - lu;
+      ws[L.dtl + i] = dtl;
+      ws[L.dtu + i] = dtu;
+      ws[L.dll + i] = dll;
+      ws[L.dlu + i] = dlu;
+      if (dtl < T(0)) a_aff = fmin(a_aff, -tl / dtl);
+      if (dtu < T(0)) a_aff = fmin(a_aff, -tu / dtu);
+      if (dll < T(0)) a_aff = fmin(a_aff, -ll / dll);
+      if (dlu < T(0)) a_aff = fmin(a_aff, -lu / dlu);
+    }
+    a_aff = warp_min(a_aff);
+    T mu_aff = T(0);
+    for (int i = lane; i < nb; i += 32) {
+      mu_aff += (ws[L.tl + i] + a_aff * ws[L.dtl + i]) * (ws[L.ll + i] + a_aff * ws[L.dll + i]) +
+                (ws[L.tu + i] + a_aff * ws[L.dtu + i]) * (ws[L.lu + i] + a_aff * ws[L.dlu + i]);
+    }
+    mu_aff = warp_sum(mu_aff) * inv2nb;
+    T sigma = mu_aff / mu;
+    sigma = sigma * sigma * sigma;
+    const T smu = sigma * mu;
+    for (int i = lane; i < nb; i += 32) {
+      const T sl = smu - ws[L.dtl + i] * ws[L.dll + i];
+      const T su = smu - ws[L.dtu + i] * ws[L.dlu + i];
+      ws[L.dr + i] = -sl / ws[L.tl + i] + su / ws[L.tu + i];
+    }
+    __syncwarp();
+    // corrector increment (vector-only re-solve), accumulated onto the predictor direction
+    delta_backward(c, ws, L, sm, lane);
+    forward_sweep<T, true>(c, ws, L, sm, lane, false, L.kffd, L.xa, L.ua);
+    T alpha = T(1e300);
+    if (sizeof(T) == 4) alpha = T(1e30);
+    for (int i = lane; i < nb; i += 32) {
+      const T tl = ws[L.tl + i], tu = ws[L.tu + i], ll = ws[L.ll + i], lu = ws[L.lu + i];
+      const T un = ws[L.ua + i];
+      const T sl = smu - ws[L.dtl + i] * ws[L.dll + i];
+      const T su = smu - ws[L.dtu + i] * ws[L.dlu + i];
+      const T dtl = un + rho * ws[L.rbl0 + i];
+      const T dtu = -un + rho * ws[L.rbu0 + i];
+      const T dll = -(ll / tl) * dtl + sl / tl - ll;
+      const T dlu = -(lu / tu) * dtu + su / tu - lu;
+      ws[L.dtl + i] = dtl;
+      ws[L.dtu + i] = dtu;
+      ws[L.dll + i] = dll;
+      ws[L.dlu + i] = dlu;
+      if (dtl < T(0)) alpha = fmin(alpha, -tl / dtl);
+      if (dtu < T(0)) alpha = fmin(alpha, -tu / dtu);
+      if (dll < T(0)) alpha = fmin(alpha, -ll / dll);
+      if (dlu < T(0)) alpha = fmin(alpha, -lu / dlu);
+    }
+    // NaN anywhere must surface: fmin drops NaNs, so test the directions explicitly
+    bool fin = true;
+    for (int i = lane; i < nb; i += 32)
+      fin = fin && finite_(ws[L.dtl + i]) && finite_(ws[L.dll + i]) && finite_(ws[L.dlu + i]);
+    if (!__all_sync(FULL, fin)) {
+      status = ST_QPFAIL;
+      break;
+    }
+    alpha = warp_min(alpha);
+    const T tau = fmax(T(0.995), T(1) - mu);
+    alpha = fmin(T(1), tau * alpha);
+    if (alpha < T(1e-12)) {
+      status = ST_MINSTEP;
+      break;
+    }
+    for (int i = lane; i < nb; i += 32) {
+      ws[L.du + i] += alpha * ws[L.ua + i];
+      ws[L.tl + i] += alpha * ws[L.dtl + i];
+      ws[L.tu + i] += alpha * ws[L.dtu + i];
+      ws[L.ll + i] += alpha * ws[L.dll + i];
+      ws[L.lu + i] += alpha * ws[L.dlu + i];
+    }
+    for (int i = lane; i < nxv; i += 32) ws[L.dx + i] += alpha * ws[L.xa + i];
+    rho *= (T(1) - alpha);
+    __syncwarp();
+  }
+  *iters = it;
+  return status;
+}
+
+// ------------------------------------------------------------------ whole solve (K1+K2+K3)
+template <typename T>
+struct SolveArgs {
+  DevCfg<T> cfg;
+  int batch;
+  const double* x0;      // [batch,13]
+  const double* yref;    // [batch,N,17]
+  const double* yref_e;  // [batch,13]
+  double* xtraj;         // warm-start store [batch,N+1,13]
+  double* utraj;         // [batch,N,4]
+  uint8_t* valid;        // [batch]
+  double* last_cmd;      // [batch,4]
+  double* u0;            // outputs (may be null)
+  int* status;
+  double* thrust;
+  double* speed;
+  int* qp_iters;
+  int* sqp_iters;
+  T* ws;                 // nslots * layout.total
+};
+
+template <typename T>
+__device__ __forceinline__ T clip_(T v, T lo, T hi) {
+  return v < lo ? lo : (v > hi ? hi : v);
+}
+
+// One PositionNMPC.solve() (controller.py:385-463) + the node's command map
+// (nodes/mpc_controller_node:124-131,152-164) for problem `prob`, executed by one warp.
+template <typename T, int NS>
+__device__ __forceinline__ void solve_one(const SolveArgs<T>& A, const WsLayout& L, T* ws, T* sm,
+                                          int prob, int lane) {
+  const DevCfg<T>& c = A.cfg;
+  const int N = c.N;
+  const int nxv = (N + 1) * NX, nuv = N * NU;
+  const double* x0 = A.x0 + (size_t)prob * NX;
+  const double* yref = A.yref + (size_t)prob * N * NZ;
+  const double* yref_e = A.yref_e + (size_t)prob * NX;
+  double* xtraj = A.xtraj + (size_t)prob * nxv;
+  double* utraj = A.utraj + (size_t)prob * nuv;
+
+  // warm start (controller.py:416-431): previous solution un-shifted with stage-0 x <- x0,
+  // or (x0, u = 0) on every stage when the previous solve is not valid.
+  const bool warm = A.valid[prob] != 0;
+  for (int i = lane; i < nxv; i += 32) {
+    const int ii = i % NX;
+    ws[L.xb + i] = (T)((warm && i >= NX) ? xtraj[i] : x0[ii]);
+  }
+  for (int i = lane; i < nuv; i += 32) ws[L.ub + i] = warm ? (T)utraj[i] : T(0);
+  __syncwarp();
+
+  int status = ST_SUCCESS;
+  int tot_qp = 0, nsqp = 0;
+  bool converged = false;
+  const int max_sqp = c.max_sqp_iter < 1 ? 1 : c.max_sqp_iter;
+  while (nsqp < max_sqp) {
+    linearize<T, NS>(c, ws, L, lane);
+    gradients(c, ws, L, yref, yref_e, lane);
+    __syncwarp();
+    int qi = 0;
+    const int qs = ipm_solve(c, ws, L, sm, lane, &qi);
+    tot_qp += qi;
+    nsqp++;
+    // acados SQP_RTI tolerates a QP that only hit its iteration cap
+    if (qs != ST_SUCCESS && qs != ST_MAXITER) {
+      status = ST_QPFAIL;
+      break;
+    }
+    __syncwarp();
+    T step = T(0);
+    bool fin = true;
+    for (int i = lane; i < nxv; i += 32) {
+      const T d = ws[L.dx + i];
+      const T v = ws[L.xb + i] + d;  // full step
+      ws[L.xb + i] = v;
+      step = fmax(step, fabs(d));
+      fin = fin && finite_(v);
+    }
+    for (int i = lane; i < nuv; i += 32) {
+      const T d = ws[L.du + i];
+      const T v = ws[L.ub + i] + d;
+      ws[L.ub + i] = v;
+      step = fmax(step, fabs(d));
+      fin = fin && finite_(v);
+    }
+    __syncwarp();
+    if (!__all_sync(FULL, fin)) {
+      status = c.nan_status;
+      break;
+    }
+    step = warp_max(step);
+    if (step <= c.sqp_tol) {
+      converged = true;
+      break;
+    }
+  }
+  if (status == ST_SUCCESS && max_sqp > 1 && !converged) status = ST_MAXITER;
+
+  // K3 epilogue: outputs, warm-start store, command mapping with last-valid fallback
+  if (status == ST_SUCCESS) {
+    for (int i = lane; i < nxv; i += 32) xtraj[i] = (double)ws[L.xb + i];
+    for (int i = lane; i < nuv; i += 32) utraj[i] = (double)ws[L.ub + i];
+  }
+  if (lane < NU) {
+    const T u = (status == ST_SUCCESS) ? ws[L.ub + lane] : T(0);
+    if (A.u0) A.u0[(size_t)prob * NU + lane] = (double)u;
+    double* last = A.last_cmd + (size_t)prob * NU;
+    const T src = (status == ST_SUCCESS) ? u : (T)last[lane];
+    const T cl = clip_(src, c.lbu[lane], c.ubu[lane]);
+    const T kf = fmax(c.kf, T(1e-9));
+    T s2 = clip_(cl / kf, T(0), c.w_max * c.w_max);
+    T sp = clip_(sqrt(s2), c.w_min, c.w_max);
+    last[lane] = (double)cl;
+    if (A.thrust) A.thrust[(size_t)prob * NU + lane] = (double)cl;
+    if (A.speed) A.speed[(size_t)prob * NU + lane] = (double)sp;
+  }
+  if (lane == 0) {
+    A.valid[prob] = (status == ST_SUCCESS) ? 1 : 0;
+    if (A.status) A.status[prob] = status;
+    if (A.qp_iters) A.qp_iters[prob] = tot_qp;
+    if (A.sqp_iters) A.sqp_iters[prob] = nsqp;
+  }
+  __syncwarp();
+}
+
+}  // namespace nmpc
