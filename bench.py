@@ -1,0 +1,393 @@
+#!/usr/bin/env python
+"""bench.py -- NMPC solves/s of the hot path on B200 (see DESIGN.md "Measurement").
+
+  python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+  python bench.py --impl reference --gpus N --steps K ...  # CPU arm (oracle port, all host cores)
+
+A *step* is one pass of the hot path over one batch: `batch` independent PositionNMPC.solve()
+calls (BASELINE.json configs[1]: 4096 hummingbirds per GPU, randomised states around hover,
+random set-point steps, N=20, cold start, SQP to convergence).  One JSON line is printed by
+rank 0.  The acados reference itself is unavailable on this box (not vendored, not
+installable), so the reference arm times the CPU oracle port of the same algorithm.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+BATCH = 4096          # per GPU (configs[1])
+HORIZON = 20
+SQP_CAP = 50          # "full SQP to convergence": step inf-norm <= 1e-8, cap 50
+SQP_TOL = 1e-8
+N_INPUT_SETS = 5      # seeds 0..4, cycled over the steps
+# algorithmic work per solve (SURVEY.md 8d / DESIGN.md): flops = S*F_LIN + I*F_IPM
+F_LIN = 0.507e6       # per SQP iteration: 20 stages x 2 steps x 2 RK stages, dense-block count
+F_IPM = 0.244e6       # per Riccati factorisation (+ predictor / corrector solves)
+BYTES_PER_SOLVE = 5752 + 2924   # compulsory HBM I/O per solve, FP64
+
+
+def load_params():
+    import yaml
+    from rotors_mpc_controller_b200.params import default_params_path
+    p = yaml.safe_load(open(default_params_path()))
+    p['solver']['horizon_steps'] = HORIZON
+    return p
+
+
+def make_inputs(seed, batch, hover):
+    from tests.problems import random_states, setpoint_refs
+    rng = np.random.default_rng(seed)
+    x0 = random_states(rng, batch)
+    yref, yref_e = setpoint_refs(rng, x0, HORIZON, hover)
+    return x0, yref, yref_e
+
+
+# ------------------------------------------------------------------ CPU arm (oracle port)
+def _cpu_worker(args):
+    seed, lo, hi, sqp = args
+    from oracle import oracle as O
+    params = load_params()
+    cfg = O.config_from_params(params, max_sqp_iter=sqp, sqp_tol=SQP_TOL)
+    hover = cfg.mass * cfg.gravity / 4.0
+    x0, yref, yref_e = make_inputs(seed, hi, hover)
+    ob = O.OracleBatch(cfg, hi - lo)
+    t0 = time.perf_counter()
+    ob.solve(x0[lo:hi], yref[lo:hi], yref_e[lo:hi])
+    return time.perf_counter() - t0, int(ob.qp_iters.sum())
+
+
+def cpu_sample(n_problems, cores, seed=0, sqp=SQP_CAP):
+    """Solve `n_problems` of the workload with the oracle, one process per core.
+    Returns (solves/s over the wall time of the parallel section, wall seconds)."""
+    import multiprocessing as mp
+    from oracle import oracle as O
+    O.build()
+    per = (n_problems + cores - 1) // cores
+    jobs = [(seed, i * per, min((i + 1) * per, n_problems), sqp) for i in range(cores)
+            if i * per < n_problems]
+    ctx = mp.get_context('fork')
+    with ctx.Pool(len(jobs)) as pool:
+        pool.map(_cpu_worker, [(seed, 0, 8, sqp)] * len(jobs))  # warm the workers
+        t0 = time.perf_counter()
+        pool.map(_cpu_worker, jobs)
+        wall = time.perf_counter() - t0
+    return n_problems / wall, wall
+
+
+def run_reference(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return 0
+    cores = os.cpu_count() or 1
+    n = 256 * cores if cores <= 32 else 128 * cores
+    times = []
+    for i in range(args.warmup + args.steps):
+        v, wall = cpu_sample(n, cores, seed=i % N_INPUT_SETS)
+        if i >= args.warmup:
+            times.append(wall)
+    value = n * len(times) / sum(times)
+    sample = (f'{n} problems per step of the configs[1] workload (cold start, SQP to '
+              f'convergence), split over {cores} processes')
+    line = {
+        'impl': 'reference', 'metric': 'NMPC solves/sec (hummingbird, N=20)', 'value': value,
+        'unit': 'solves/s', 'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
+        'ms_per_step': 1e3 * sum(times) / len(times), 'higher_is_better': True,
+        'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
+        'config': workload_config(args.gpus),
+        'cpu_baseline': {'value': value, 'unit': 'solves/s', 'cores': cores, 'kind': 'port',
+                         'sample': sample},
+        'e2e': {'value': value, 'unit': 'solves/s', 'h2d_bytes_per_step': 0,
+                'd2h_bytes_per_step': 0},
+        'note': 'acados/HPIPM (the true reference implementation) is unavailable on this box; '
+                'this arm times oracle/ (C port of the same algorithm), one process per core',
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def workload_config(gpus):
+    return {'workload': 'configs[1]: batch 4096 hummingbirds per GPU, randomised states around '
+                        'hover, random set-point steps, N=20, dt=0.05, cold start, SQP to '
+                        'convergence (step<=1e-8, cap 50), ERK midpoint x2, u-box [0.0214,6.003] N',
+            'batch_per_gpu': BATCH, 'horizon': HORIZON, 'global_batch': BATCH * gpus,
+            'parallelism': f'batch-sharded x{gpus}, no data-path collective',
+            'l2': 'flushed between timed steps (256 MiB write, outside the event pair)'}
+
+
+# ------------------------------------------------------------------ clocks sampler
+class ClockSampler:
+    Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,'
+         'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
+         'clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ['nvidia-smi', f'--query-gpu={self.Q}', '--format=csv,noheader,nounits',
+                 '-i', str(self.index), '-lms', '100'], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(',')])
+
+    def stop(self):
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+                for n, v in zip(names, r[2:6]):
+                    if v.lower().startswith('active'):
+                        reasons.add(n)
+            except Exception:
+                pass
+        return {'sm_mhz': float(np.median(sm)) if sm else None,
+                'sm_max_mhz': max(mx) if mx else None, 'reasons': sorted(reasons),
+                'samples': len(sm)}
+
+
+# ------------------------------------------------------------------ GPU arm
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py: no CUDA device (the product path has no CPU fallback)')
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        dist.init_process_group('nccl', device_id=dev)
+
+    import __graft_entry__ as entry
+    if rank == 0:
+        entry.build()
+    if world > 1:
+        dist.barrier()
+    from rotors_mpc_controller_b200 import BatchedPositionNMPC, _abi
+    params = load_params()
+    params['solver']['max_sqp_iter'] = SQP_CAP
+    params['solver']['sqp_tol'] = SQP_TOL
+    ctl = BatchedPositionNMPC(params, batch=BATCH, device=local)
+    hover = ctl.hover_thrust
+
+    # inputs: N_INPUT_SETS seeded batches per rank, resident in HBM and in pinned host memory
+    dev_in, host_in = [], []
+    for s in range(N_INPUT_SETS):
+        arrs = make_inputs(1000 * rank + s, BATCH, hover)
+        dev_in.append(tuple(torch.as_tensor(a, device=dev) for a in arrs))
+        pinned = []
+        for a in arrs:
+            t = torch.empty(a.shape, dtype=torch.float64, pin_memory=True)
+            t.numpy()[...] = a
+            pinned.append(t.numpy())
+        host_in.append(tuple(pinned))
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def one_step(i, timed):
+        x0, yref, yref_e = dev_in[i % N_INPUT_SETS]
+        ctl.invalidate()          # cold start every step: each step is a fresh batch
+        flush.zero_()             # evict the previous step's data from L2
+        torch.cuda.synchronize(dev)
+        if timed:
+            e0 = torch.cuda.Event(enable_timing=True)
+            e1 = torch.cuda.Event(enable_timing=True)
+            e0.record()
+            u0, st = ctl.solve(x0, yref, yref_e)
+            e1.record()
+            torch.cuda.synchronize(dev)
+            return e0.elapsed_time(e1), st
+        u0, st = ctl.solve(x0, yref, yref_e)
+        torch.cuda.synchronize(dev)
+        return 0.0, st
+
+    W, K = max(args.warmup, 3), args.steps
+    for i in range(W):
+        one_step(i, False)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    launches0 = ctl.kernel_launches
+    step_ms, qp_sum, sqp_sum, ok_count = [], 0, 0, 0
+    wall0 = time.perf_counter()
+    for i in range(K):
+        ms, st = one_step(W + i, True)
+        step_ms.append(ms)
+        stats = ctl.stats()
+        qp_sum += int(stats['qp_iters'].sum())
+        sqp_sum += int(stats['sqp_iters'].sum())
+        ok_count += int((st == 0).sum().item())
+    barrier()
+    wall = time.perf_counter() - wall0
+    launches = ctl.kernel_launches - launches0
+    total_ms = float(sum(step_ms))
+
+    # end-to-end through the public host API: pinned host buffers, H2D + solve + D2H per step
+    e2e_t = []
+    for i in range(W + K):
+        x0, yref, yref_e = host_in[i % N_INPUT_SETS]
+        ctl.invalidate()
+        flush.zero_()
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+        u0h, sth = ctl.solve(x0, yref, yref_e)     # returns after the D2H copies completed
+        t1 = time.perf_counter()
+        if i >= W:
+            e2e_t.append(t1 - t0)
+    e2e_total = float(sum(e2e_t))
+    clocks = sampler.stop() if rank == 0 else None
+
+    if world > 1:
+        t = torch.tensor([total_ms, e2e_total], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms, e2e_total = float(t[0]), float(t[1])
+        c = torch.tensor([qp_sum, sqp_sum, ok_count, launches], dtype=torch.int64, device=dev)
+        dist.all_reduce(c, op=dist.ReduceOp.SUM)
+        qp_sum, sqp_sum, ok_count, launches = (int(v) for v in c)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    n_solves = world * BATCH * K
+    value = n_solves / (total_ms * 1e-3)
+    e2e_value = n_solves / e2e_total
+    mean_qp = qp_sum / n_solves
+    mean_sqp = sqp_sum / n_solves
+    # roofline of the (single, fused) kernel; launch duration = CUDA-event time of the step
+    launch_s = (total_ms * 1e-3) / K
+    flops_per_launch = BATCH * (mean_sqp * F_LIN + mean_qp * F_IPM)
+    bytes_per_launch = BATCH * BYTES_PER_SOLVE
+    peaks = {}
+    try:
+        peaks = json.load(open(ROOT / 'MEASURED_PEAKS.json'))
+    except Exception:
+        pass
+    hbm_peak = float(peaks.get('hbm_gbs', 6650.0))
+    import ctypes as C
+    tf = C.c_double(0.0)
+    _abi.check(_abi.lib().nmpc_fp64_peak(local, C.byref(tf)), 'nmpc_fp64_peak')
+    achieved_gbs = bytes_per_launch / launch_s * 1e-9
+    achieved_tf = flops_per_launch / launch_s * 1e-12
+    line = {
+        'metric': 'NMPC solves/sec (hummingbird, N=20)', 'value': value, 'unit': 'solves/s',
+        'n_gpus': world, 'steps': K, 'warmup': W, 'ms_per_step': total_ms / K,
+        'p50_batch_latency_ms': float(np.median(step_ms)),
+        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64',
+        'data': 'synthetic', 'config': workload_config(world),
+        'clocks': clocks,
+        'e2e': {'value': e2e_value, 'unit': 'solves/s',
+                'h2d_bytes_per_step': BATCH * (13 + HORIZON * 17 + 13) * 8,
+                'd2h_bytes_per_step': BATCH * (3 * 4 * 8 + 4)},
+        'gpu_launches': launches,
+        'roofline': {'bound': 'hbm', 'achieved': achieved_gbs, 'peak': hbm_peak, 'unit': 'GB/s',
+                     'frac': achieved_gbs / hbm_peak, 'traffic': None,
+                     'peak_source': 'MEASURED_PEAKS.json' if peaks else 'fallback',
+                     'note': 'compulsory I/O only (8.7 KB/solve); the kernel is FP64-pipe / '
+                             'shared-memory / latency bound, see roofline_fp64'},
+        'roofline_fp64': {'bound': 'fp64', 'achieved': achieved_tf, 'peak': tf.value,
+                          'unit': 'TFLOP/s', 'frac': achieved_tf / tf.value if tf.value else None,
+                          'peak_source': 'nmpc_fp64_peak DFMA micro-benchmark, same run',
+                          'flops_per_solve': flops_per_launch / BATCH},
+        'solver_stats': {'mean_sqp_iters': mean_sqp, 'mean_riccati_factorisations': mean_qp,
+                         'status_ok_frac': ok_count / n_solves},
+        'wall_s_timed_region': wall,
+    }
+    if world == 1 and not args.no_cpu:
+        cores = os.cpu_count() or 1
+        n = 256 * cores if cores <= 32 else 128 * cores
+        v, w = cpu_sample(n, cores, seed=0)
+        line['cpu_baseline'] = {
+            'value': v, 'unit': 'solves/s', 'cores': cores, 'kind': 'port',
+            'sample': f'{n} problems of the same workload (seed 0), oracle/ C port, one process '
+                      f'per core, {w:.1f} s wall'}
+    if args.extras and world == 1:
+        line['extras'] = extras(params, dev)
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def extras(params, dev):
+    """RTI throughput at large batch (not the headline workload; reported for context)."""
+    import copy
+    import torch
+    from rotors_mpc_controller_b200 import BatchedPositionNMPC
+    from tests.problems import aggressive
+    out = {}
+    p = copy.deepcopy(params)
+    p['solver']['max_sqp_iter'] = 1
+    B = 65536
+    ctl = BatchedPositionNMPC(p, batch=B, device=dev.index)
+    for name in ('rti_cfg2_cold', 'rti_aggressive_cold'):
+        rng = np.random.default_rng(0)
+        if name == 'rti_cfg2_cold':
+            arrs = make_inputs(0, B, ctl.hover_thrust)
+        else:
+            arrs = aggressive(rng, B, HORIZON, ctl.hover_thrust)
+        X, Y, Z = (torch.as_tensor(a, device=dev) for a in arrs)
+        ms = []
+        for rep in range(6):
+            ctl.invalidate()
+            torch.cuda.synchronize(dev)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            ctl.solve(X, Y, Z)
+            e1.record()
+            torch.cuda.synchronize(dev)
+            ms.append(e0.elapsed_time(e1))
+        it = ctl.stats()['qp_iters']
+        out[name] = {'batch': B, 'solves_per_s': B / (np.median(ms[1:]) * 1e-3),
+                     'ms': float(np.median(ms[1:])), 'mean_factorisations': float(it.mean()),
+                     'max_factorisations': int(it.max())}
+    ctl.close()
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=40)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
+    ap.add_argument('--extras', action='store_true', help='add large-batch RTI numbers')
+    args = ap.parse_args()
+    if args.impl == 'reference':
+        return run_reference(args)
+    return run_gpu(args)
+
+
+if __name__ == '__main__':
+    sys.exit(main())

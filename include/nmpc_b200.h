@@ -129,6 +129,10 @@ int nmpc_set_trajectories(nmpc_handle_t *h, const double *xtraj, const double *u
 int nmpc_discretize_device(nmpc_handle_t *h, int32_t n, const double *x, const double *u,
                            double *xn, double *A, double *B, void *stream);
 
+/* Measured DFMA throughput of `device` in TFLOP/s (8 independent FMA chains per thread,
+ * best of 4): the FP64 roofline denominator used by bench.py. */
+int nmpc_fp64_peak(int32_t device, double *tflops);
+
 /* Introspection */
 int nmpc_batch(const nmpc_handle_t *h);
 int nmpc_horizon(const nmpc_handle_t *h);

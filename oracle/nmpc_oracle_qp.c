@@ -6,6 +6,9 @@
  * its primal optimum is unique and any tightly converged solver pins it.
  */
 #include <math.h>
+#ifdef ORC_TRACE
+#include <stdio.h>
+#endif
 #include <stdlib.h>
 #include <string.h>
 
@@ -282,6 +285,12 @@ static void riccati_delta_solve(const orc_qp *qp, const double *dr, const ric_ws
 }
 
 /* ------------------------------------------------------- interior point */
+/* Weight of Mehrotra's second-order term.  With a short affine step the full term
+ * dt_aff*dlam_aff over-corrects and the iteration can fall into a 2-cycle (seen on warm
+ * re-solves with many active bounds); scaling it by min(1, 2 alpha_aff) removes the cycle at
+ * no measurable cost in iterations. */
+static double corr_weight(double a) { return fmin(1.0, 2.0 * a); }
+
 /* Mehrotra predictor-corrector on
  *     min 1/2 z'Hz + g'z   s.t. dynamics,  lb <= du <= ub
  * with slacks t_l = du - lb, t_u = ub - du and multipliers lam_l, lam_u >= 0.
@@ -399,18 +408,19 @@ int orc_qp_solve(const orc_qp *qp, int iter_max, double tol, double *dx, double 
     mu_aff /= (double)(2 * nb);
     double sigma = mu_aff / mu;
     sigma = sigma * sigma * sigma;
+    const double CORRW = corr_weight(alpha_aff);
     /* corrector increment: only the input gradient changes */
     for (int i = 0; i < nb; i++) {
-      const double sl = sigma * mu - dtl[i] * dll[i];
-      const double su = sigma * mu - dtu[i] * dlu[i];
+      const double sl = sigma * mu - CORRW * dtl[i] * dll[i];
+      const double su = sigma * mu - CORRW * dtu[i] * dlu[i];
       dr[i] = -sl / t_l[i] + su / t_u[i];
     }
     riccati_delta_solve(qp, dr, &ws, xc, uc, kffd);
     double alpha = 1e300; /* longest step keeping t, lam >= 0 (not capped at 1 yet) */
     for (int i = 0; i < nb; i++) {
       const double un = ua[i] + uc[i];
-      const double sl = sigma * mu - dtl[i] * dll[i];
-      const double su = sigma * mu - dtu[i] * dlu[i];
+      const double sl = sigma * mu - CORRW * dtl[i] * dll[i];
+      const double su = sigma * mu - CORRW * dtu[i] * dlu[i];
       dtl[i] = un + rho * rbl0[i];
       dtu[i] = -un + rho * rbu0[i];
       dll[i] = -(lam_l[i] / t_l[i]) * dtl[i] + sl / t_l[i] - lam_l[i];
@@ -420,6 +430,19 @@ int orc_qp_solve(const orc_qp *qp, int iter_max, double tol, double *dx, double 
       if (dll[i] < 0) alpha = fmin(alpha, -lam_l[i] / dll[i]);
       if (dlu[i] < 0) alpha = fmin(alpha, -lam_u[i] / dlu[i]);
     }
+#ifdef ORC_TRACE
+    {
+      double tmin = 1e300, lmin = 1e300, cmin = 1e300, cmax = 0;
+      for (int i = 0; i < nb; i++) {
+        tmin = fmin(tmin, fmin(t_l[i], t_u[i]));
+        lmin = fmin(lmin, fmin(lam_l[i], lam_u[i]));
+        cmin = fmin(cmin, fmin(t_l[i] * lam_l[i], t_u[i] * lam_u[i]));
+        cmax = fmax(cmax, fmax(t_l[i] * lam_l[i], t_u[i] * lam_u[i]));
+      }
+      fprintf(stderr, "it %d mu %.3e mu_aff %.3e sig %.2e a_aff %.2e amax %.3e rho %.2e tmin %.1e lmin %.1e cmin %.1e cmax %.1e\n",
+              it, mu, mu_aff, sigma, alpha_aff, alpha, rho, tmin, lmin, cmin, cmax);
+    }
+#endif
     if (!(alpha == alpha)) {
       status = ORC_QP_FAILURE;
       break;

@@ -55,6 +55,7 @@ SYMBOLS = {
     'nmpc_get_stats': (C.c_int, [_vp, _ip, _ip, C.c_int32]),
     'nmpc_set_trajectories': (C.c_int, [_vp, _dp, _dp, _bp]),
     'nmpc_discretize_device': (C.c_int, [_vp, C.c_int32, _dp, _dp, _dp, _dp, _dp, _vp]),
+    'nmpc_fp64_peak': (C.c_int, [C.c_int32, C.POINTER(C.c_double)]),
     'nmpc_batch': (C.c_int, [_vp]),
     'nmpc_horizon': (C.c_int, [_vp]),
     'nmpc_workspace_bytes': (C.c_int64, [_vp]),

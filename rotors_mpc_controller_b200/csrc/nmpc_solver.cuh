@@ -570,9 +570,11 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
     T sigma = mu_aff / mu;
     sigma = sigma * sigma * sigma;
     const T smu = sigma * mu;
+    // weight of the second-order term: min(1, 2 alpha_aff) (breaks Mehrotra 2-cycles)
+    const T cw = fmin(T(1), T(2) * a_aff);
     for (int i = lane; i < nb; i += 32) {
-      const T sl = smu - ws[L.dtl + i] * ws[L.dll + i];
-      const T su = smu - ws[L.dtu + i] * ws[L.dlu + i];
+      const T sl = smu - cw * ws[L.dtl + i] * ws[L.dll + i];
+      const T su = smu - cw * ws[L.dtu + i] * ws[L.dlu + i];
       ws[L.dr + i] = -sl / ws[L.tl + i] + su / ws[L.tu + i];
     }
     __syncwarp();
@@ -584,8 +586,8 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
     for (int i = lane; i < nb; i += 32) {
       const T tl = ws[L.tl + i], tu = ws[L.tu + i], ll = ws[L.ll + i], lu = ws[L.lu + i];
       const T un = ws[L.ua + i];
-      const T sl = smu - ws[L.dtl + i] * ws[L.dll + i];
-      const T su = smu - ws[L.dtu + i] * ws[L.dlu + i];
+      const T sl = smu - cw * ws[L.dtl + i] * ws[L.dll + i];
+      const T su = smu - cw * ws[L.dtu + i] * ws[L.dlu + i];
       const T dtl = un + rho * ws[L.rbl0 + i];
       const T dtu = -un + rho * ws[L.rbu0 + i];
       const T dll = -(ll / tl) * dtl + sl / tl - ll;
