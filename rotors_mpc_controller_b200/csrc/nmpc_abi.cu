@@ -15,12 +15,16 @@ using namespace nmpc;
 namespace {
 
 constexpr int WARPS = 4;  // warps (= problems in flight) per CTA; warps never synchronise
+#ifndef NMPC_MIN_CTAS
+#define NMPC_MIN_CTAS 3
+#endif
+constexpr int MIN_CTAS = NMPC_MIN_CTAS;  // register cap: 65536 / (128 * MIN_CTAS) per thread
 
 constexpr int smem_elems_per_warp() { return (SmemLayout::total + 3) & ~3; }
 
 // ---------------------------------------------------------------- kernels
 template <typename T, int NS>
-__global__ void __launch_bounds__(WARPS * 32)
+__global__ void __launch_bounds__(WARPS * 32, MIN_CTAS)
     nmpc_solve_kernel(const __grid_constant__ SolveArgs<T> A, const __grid_constant__ WsLayout L,
                       int* __restrict__ work_counter) {
   extern __shared__ __align__(16) unsigned char smem_raw[];

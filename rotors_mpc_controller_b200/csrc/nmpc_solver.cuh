@@ -28,26 +28,26 @@ enum : int { ST_SUCCESS = 0, ST_NAN = 1, ST_MAXITER = 2, ST_MINSTEP = 3, ST_QPFA
 // Offsets (in elements of T) inside one workspace slot.
 struct WsLayout {
   int N;
-  size_t M, K, Qi, kff, kffd;
-  size_t xb, q, b, dx, xa;                                            // x-type vectors
-  size_t ub, r, lb, ubd, du, ua, tl, tu, ll, lu, rbl0, rbu0, ru0;    // u-type vectors
-  size_t dtl, dtu, dll, dlu, Rt, rt, dr;
-  size_t total;
+  int M, K, Qi, kff, kffd;
+  int xb, q, b, dx, xa;                                            // x-type vectors
+  int ub, r, lb, ubd, du, ua, tl, tu, ll, lu, rbl0, rbu0, ru0;    // u-type vectors
+  int dtl, dtu, dll, dlu, Rt, rt, dr;
+  int total;
 };
 
 __host__ __device__ inline WsLayout make_layout(int N) {
   WsLayout L;
   L.N = N;
-  size_t o = 0;
-  auto take = [&](size_t n) {
-    size_t r = o;
-    o += (n + 3) & ~size_t(3);  // keep 32-byte alignment for T = double
+  int o = 0;
+  auto take = [&](int n) {
+    int r = o;
+    o += (n + 3) & ~3;  // keep 32-byte alignment for T = double
     return r;
   };
-  const size_t nx = (size_t)(N + 1) * NX, nu = (size_t)N * NU;
-  L.M = take((size_t)N * NX * NZ);
-  L.K = take((size_t)N * NU * NX);
-  L.Qi = take((size_t)N * 16);
+  const int nx = (N + 1) * NX, nu = N * NU;
+  L.M = take(N * NX * NZ);
+  L.K = take(N * NU * NX);
+  L.Qi = take(N * 16);
   L.kff = take(nu);
   L.kffd = take(nu);
   L.xb = take(nx);
@@ -190,7 +190,7 @@ __device__ __forceinline__ void linearize(const DevCfg<T>& c, T* __restrict__ ws
     erk_column<T, NS>(c, x, u, s, su);
     if (lane < NZ) {
 #pragma unroll
-      for (int i = 0; i < NX; i++) M[((size_t)k * NX + i) * NZ + lane] = s[i];
+      for (int i = 0; i < NX; i++) M[(k * NX + i) * NZ + lane] = s[i];
     }
 #pragma unroll
     for (int i = 0; i < NX; i++)
@@ -208,245 +208,24 @@ __device__ __forceinline__ void gradients(const DevCfg<T>& c, T* __restrict__ ws
   const T* ub = ws + L.ub;
   for (int idx = lane; idx < N * NX; idx += 32) {
     const int k = idx / NX, i = idx - k * NX;
-    ws[L.q + idx] = c.Wq[i] * (xb[idx] - (T)yref[(size_t)k * NZ + i]);
+    ws[L.q + idx] = c.Wq[i] * (xb[idx] - (T)yref[k * NZ + i]);
   }
   if (lane < NX) ws[L.q + N * NX + lane] = c.We[lane] * (xb[N * NX + lane] - (T)yref_e[lane]);
   for (int idx = lane; idx < N * NU; idx += 32) {
     const int k = idx >> 2, a = idx & 3;
     const T u = ub[idx];
-    ws[L.r + idx] = c.Wr[a] * (u - (T)yref[(size_t)k * NZ + NX + a]);
+    ws[L.r + idx] = c.Wr[a] * (u - (T)yref[k * NZ + NX + a]);
     ws[L.lb + idx] = c.lbu[a] - u;
     ws[L.ubd + idx] = c.ubu[a] - u;
     ws[L.Rt + idx] = c.Rd[a];
   }
 }
 
-// ------------------------------------------------------------------ K2: Riccati factorisation
-// Backward sweep with input Hessian diagonal Rt and input gradient rt (both N x 4 in the
-// workspace), fused with the right-hand side (rho*b, rho*q, rt); rho is 1 for the
-// equality-constrained phase-0 solve and 0 afterwards (see ipm_solve).  Writes K_k, Quu_k^-1
-// and the feed-forward k_k per stage.  Returns false on a non-positive pivot / NaN.
-template <typename T>
-__device__ __forceinline__ bool factor_sweep(const DevCfg<T>& c, T* __restrict__ ws,
-                                             const WsLayout& L, T* __restrict__ sm, int lane,
-                                             bool rho1) {
-  const int N = c.N;
-  T* sP = sm + SmemLayout::P;
-  T* sM = sm + SmemLayout::M;
-  T* sK = sm + SmemLayout::K;
-  T* sp = sm + SmemLayout::p;
-  T* swv = rho1 ? (sm + SmemLayout::wv) : sp;
-  const int jx = lane - NU;                 // state index owned by an x-lane
-  const bool xlane = (lane >= NU) && (lane < NZ);
-  const bool active = lane < NZ;
-  bool ok = true;
+}  // namespace nmpc
 
-  // terminal cost-to-go: P = diag(QN), p = rho * q_N
-  if (xlane) {
-#pragma unroll
-    for (int i = 0; i < NX; i++) sP[jx * SP_LD + i] = (i == jx) ? c.QN[jx] : T(0);
-    sp[jx] = rho1 ? ws[L.q + (size_t)N * NX + jx] : T(0);
-  }
-  __syncwarp();
+#include "nmpc_riccati.cuh"
 
-  for (int k = N - 1; k >= 0; k--) {
-    const T* Mk = ws + L.M + (size_t)k * NX * NZ;
-    // 1. this lane's column of M_k (coalesced row-major reads), staged to shared memory
-    T m[NX];
-    if (active) {
-#pragma unroll
-      for (int i = 0; i < NX; i++) {
-        m[i] = Mk[i * NZ + lane];
-        sM[i * SM_LD + lane] = m[i];
-      }
-    } else {
-#pragma unroll
-      for (int i = 0; i < NX; i++) m[i] = T(0);
-    }
-    if (rho1 && xlane) {  // wv = P b_k + p
-      T s = sp[jx];
-#pragma unroll
-      for (int cc = 0; cc < NX; cc++) s += sP[jx * SP_LD + cc] * ws[L.b + (size_t)k * NX + cc];
-      swv[jx] = s;
-    }
-    // 2. w = P m   (P broadcast from shared memory)
-    T w[NX];
-#pragma unroll
-    for (int i = 0; i < NX; i++) {
-      T s = T(0);
-#pragma unroll
-      for (int cc = 0; cc < NX; cc++) s += sP[i * SP_LD + cc] * m[cc];
-      w[i] = s;
-    }
-    __syncwarp();
-    // 3. G(:,j) = M' w  and  g_j = m . wv + gradient_j
-    T G[NZ];
-#pragma unroll
-    for (int i = 0; i < NZ; i++) G[i] = T(0);
-#pragma unroll
-    for (int r = 0; r < NX; r++) {
-#pragma unroll
-      for (int i = 0; i < NZ; i++) G[i] += sM[r * SM_LD + i] * w[r];
-    }
-    T g = T(0);
-#pragma unroll
-    for (int r = 0; r < NX; r++) g += m[r] * swv[r];
-    if (lane < NU) {
-      g += ws[L.rt + (size_t)k * NU + lane];
-    } else if (xlane && rho1) {
-      g += ws[L.q + (size_t)k * NX + jx];
-    }
-    {
-      T d = T(0);
-      if (lane < NU) d = ws[L.Rt + (size_t)k * NU + lane];
-      else if (xlane) d = c.Qd[jx];
-#pragma unroll
-      for (int i = 0; i < NZ; i++)
-        if (i == lane) G[i] += d;
-    }
-    // 4. Quu (lanes 0..3 hold its columns) -> every lane; inverse computed redundantly
-    T Quu[4][4], Qi[4][4];
-#pragma unroll
-    for (int i = 0; i < 4; i++)
-#pragma unroll
-      for (int a = 0; a <= i; a++) {
-        Quu[i][a] = __shfl_sync(FULL, G[i], a);
-        Quu[a][i] = Quu[i][a];
-      }
-    ok = spd4_inverse(Quu, Qi) && ok;
-    T gu[4], kf[4];
-#pragma unroll
-    for (int a = 0; a < 4; a++) gu[a] = __shfl_sync(FULL, g, a);
-#pragma unroll
-    for (int a = 0; a < 4; a++) {
-      T s = T(0);
-#pragma unroll
-      for (int l = 0; l < 4; l++) s -= Qi[a][l] * gu[l];
-      kf[a] = s;
-    }
-    // 5. feedback column K(:,jx) = -Quu^-1 Qux(:,jx)
-    if (xlane) {
-#pragma unroll
-      for (int a = 0; a < 4; a++) {
-        T s = T(0);
-#pragma unroll
-        for (int l = 0; l < 4; l++) s -= Qi[a][l] * G[l];
-        sK[a * SP_LD + jx] = s;
-        ws[L.K + ((size_t)k * NU + a) * NX + jx] = s;
-      }
-    }
-    if (lane < NU) {
-#pragma unroll
-      for (int a = 0; a < 4; a++)
-        if (a == lane) {
-          ws[L.kff + (size_t)k * NU + a] = kf[a];
-#pragma unroll
-          for (int l = 0; l < 4; l++) ws[L.Qi + (size_t)k * 16 + a * 4 + l] = Qi[a][l];
-        }
-    }
-    __syncwarp();
-    // 6. cost-to-go row jx:  P(jx,:) = Qxx(jx,:) + Qux(:,jx)' K ,  p_jx = g + Qux(:,jx)' k
-    if (xlane && k > 0) {
-      T pn = g;
-#pragma unroll
-      for (int a = 0; a < 4; a++) pn += G[a] * kf[a];
-#pragma unroll
-      for (int i = 0; i < NX; i++) {
-        T s = G[NU + i];
-#pragma unroll
-        for (int a = 0; a < 4; a++) s += G[a] * sK[a * SP_LD + i];
-        sP[jx * SP_LD + i] = s;
-      }
-      sp[jx] = pn;
-    }
-    __syncwarp();
-  }
-  return ok;
-}
-
-// Forward roll-out  u_k = K_k x_k + kf_k,  x_{k+1} = A_k x_k + B_k u_k + rho b_k  from x_0 = 0.
-// kf points at kff (factor sweep) or kffd (delta sweep).  ACC: add into outX/outU.
-template <typename T, bool ACC>
-__device__ __forceinline__ void forward_sweep(const DevCfg<T>& c, T* __restrict__ ws,
-                                              const WsLayout& L, T* __restrict__ sm, int lane,
-                                              bool rho1, size_t kf_off, size_t outX, size_t outU) {
-  const int N = c.N;
-  T* sxa = sm + SmemLayout::xA;
-  T* sxb = sm + SmemLayout::xB;
-  T* su = sm + SmemLayout::u;
-  if (lane < NX) {
-    sxa[lane] = T(0);
-    if (!ACC) ws[outX + lane] = T(0);
-  }
-  __syncwarp();
-  for (int k = 0; k < N; k++) {
-    T* xin = (k & 1) ? sxb : sxa;
-    T* xout = (k & 1) ? sxa : sxb;
-    if (lane < NU) {
-      const T* Kr = ws + L.K + ((size_t)k * NU + lane) * NX;
-      T s = ws[kf_off + (size_t)k * NU + lane];
-#pragma unroll
-      for (int j = 0; j < NX; j++) s += Kr[j] * xin[j];
-      su[lane] = s;
-      if (ACC) ws[outU + (size_t)k * NU + lane] += s;
-      else ws[outU + (size_t)k * NU + lane] = s;
-    }
-    __syncwarp();
-    if (lane < NX) {
-      const T* Mr = ws + L.M + ((size_t)k * NX + lane) * NZ;
-      T s = rho1 ? ws[L.b + (size_t)k * NX + lane] : T(0);
-#pragma unroll
-      for (int a = 0; a < NU; a++) s += Mr[a] * su[a];
-#pragma unroll
-      for (int j = 0; j < NX; j++) s += Mr[NU + j] * xin[j];
-      xout[lane] = s;
-      if (ACC) ws[outX + (size_t)(k + 1) * NX + lane] += s;
-      else ws[outX + (size_t)(k + 1) * NX + lane] = s;
-    }
-    __syncwarp();
-  }
-}
-
-// Backward sweep for a right-hand side that differs only in the input gradient (b = 0, q = 0,
-// r = dr): reuses K_k and Quu_k^-1, writes the feed-forward kffd_k.
-template <typename T>
-__device__ __forceinline__ void delta_backward(const DevCfg<T>& c, T* __restrict__ ws,
-                                               const WsLayout& L, T* __restrict__ sm, int lane) {
-  const int N = c.N;
-  T* sp = sm + SmemLayout::p;
-  const int jx = lane - NU;
-  const bool xlane = (lane >= NU) && (lane < NZ);
-  if (lane < NX) sp[lane] = T(0);
-  __syncwarp();
-  for (int k = N - 1; k >= 0; k--) {
-    const T* Mk = ws + L.M + (size_t)k * NX * NZ;
-    T gz = T(0);
-    if (lane < NZ) {
-#pragma unroll
-      for (int r = 0; r < NX; r++) gz += Mk[r * NZ + lane] * sp[r];
-      if (lane < NU) gz += ws[L.dr + (size_t)k * NU + lane];
-    }
-    T gu[4];
-#pragma unroll
-    for (int a = 0; a < 4; a++) gu[a] = __shfl_sync(FULL, gz, a);
-    if (lane < NU) {
-      const T* Qr = ws + L.Qi + (size_t)k * 16 + lane * 4;
-      T s = T(0);
-#pragma unroll
-      for (int l = 0; l < 4; l++) s -= Qr[l] * gu[l];
-      ws[L.kffd + (size_t)k * NU + lane] = s;
-    }
-    T pn = gz;
-    if (xlane) {
-#pragma unroll
-      for (int a = 0; a < 4; a++) pn += ws[L.K + ((size_t)k * NU + a) * NX + jx] * gu[a];
-    }
-    __syncwarp();
-    if (xlane) sp[jx] = pn;
-    __syncwarp();
-  }
-}
-
+namespace nmpc {
 // ------------------------------------------------------------------ K2: interior point
 // Mehrotra predictor-corrector for   min 1/2 z'Hz + g'z  s.t. dynamics, lb <= du <= ub.
 //  phase 0: equality-constrained solve; if it respects the box it is the optimum (strictly

@@ -1,5 +1,5 @@
 import sys, time, numpy as np, torch, yaml
-sys.path.insert(0, '.')
+sys.path.insert(0, '.'); sys.path.insert(0, '..')
 from rotors_mpc_controller_b200 import BatchedPositionNMPC
 from rotors_mpc_controller_b200.params import default_params_path
 from tests.problems import random_states, setpoint_refs, aggressive
