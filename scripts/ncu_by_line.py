@@ -73,12 +73,20 @@ print('--- innermost top 25')
 for (f, ln), s in inner.most_common(25):
     print(f'  {f}:{ln}  {100.0 * s / tot:5.1f}%')
 
+import os
+BOUNDS = [10 ** 9, 10 ** 9]
+_ric = os.path.join(os.path.dirname(os.path.abspath(__file__)), '..', 'rotors_mpc_controller_b200', 'csrc', 'nmpc_riccati.cuh')
+for _i, _l in enumerate(open(_ric), 1):
+    if 'void forward_sweep' in _l:
+        BOUNDS[0] = _i - 8
+    if 'void delta_backward' in _l:
+        BOUNDS[1] = _i - 4
 # coarse buckets: which function of nmpc_riccati.cuh / nmpc_solver.cuh the samples fall in
 def bucket(ch):
     for fr in reversed(ch):
         if fr[0] == 'nmpc_riccati.cuh':
             ln = fr[1]
-            return 'factor_sweep' if ln < 178 else ('forward_sweep' if ln < 264 else 'delta_backward')
+            return 'factor_sweep' if ln < BOUNDS[0] else ('forward_sweep' if ln < BOUNDS[1] else 'delta_backward')
     for fr in reversed(ch):
         if fr[0] == 'nmpc_solver.cuh' and fr[1] < 225:
             return 'linearize/gradients/helpers'

@@ -247,3 +247,64 @@ def test_long_horizon(params, O):
     ur, sr, _, _ = ob.solve(x0, yref, yref_e)
     assert np.array_equal(st, sr)
     assert np.max(np.abs(u0 - ur)) < 1e-7
+
+
+def test_committed_goldens(params):
+    """CUDA path against tests/golden/nmpc_golden.npz (made by tests/golden/make_golden.py)."""
+    from pathlib import Path
+    g = np.load(Path(__file__).parent / 'golden' / 'nmpc_golden.npz')
+    ctl, _ = _mk(params, 6)
+    xn, A, B = ctl.discretize(g['disc_x'], g['disc_u'])
+    assert np.max(np.abs(xn - g['disc_mid_xn'])) < 1e-12
+    assert np.max(np.abs(A - g['disc_mid_A'])) < 1e-12 and np.max(np.abs(B - g['disc_mid_B'])) < 1e-12
+    ctl, _ = _mk(params, 16)
+    u, s = ctl.solve(g['b_x0'], g['b_yref'], g['b_yref_e'])
+    assert np.array_equal(s, g['b_status_cold']) and np.max(np.abs(u - g['b_u0_cold'])) < TOL_U
+    assert np.max(np.abs(ctl.trajectories()[0] - g['b_xtraj_cold'])) < TOL_U
+    u, s = ctl.solve(g['b_x0'], g['b_yref'], g['b_yref_e'])
+    assert np.max(np.abs(u - g['b_u0_warm'])) < TOL_U
+    th, sp = ctl.command()
+    assert np.max(np.abs(th - g['b_thrust_warm'])) < TOL_U
+    assert np.max(np.abs(sp - g['b_speed_warm'])) < 1e-5
+    ctl, _ = _mk(params, 16)
+    u, s = ctl.solve(g['a_x0'], g['a_yref'], g['a_yref_e'])
+    assert np.array_equal(s, g['a_status']) and np.max(np.abs(u - g['a_u0'])) < TOL_U
+    assert np.max(np.abs(ctl.trajectories()[1] - g['a_utraj'])) < TOL_U
+    assert np.array_equal(ctl.stats()['qp_iters'], g['a_iters'])
+    ctl, _ = _mk(params, 8, max_sqp_iter=50, sqp_tol=1e-8)
+    u, s = ctl.solve(g['s_x0'], g['s_yref'], g['s_yref_e'])
+    assert np.array_equal(s, g['s_status']) and np.max(np.abs(u - g['s_u0'])) < 1e-6
+    # cfg1 closed loop replayed open-loop on the recorded states (warm start carried along)
+    from rotors_mpc_controller_b200 import BatchedPositionNMPC
+    one = BatchedPositionNMPC(params, batch=1)
+    for k in range(g['cfg1_x'].shape[0]):
+        u, s = one.solve(g['cfg1_x'][k][None], g['cfg1_yref'][None], g['cfg1_yref_e'][None])
+        assert s[0] == 0 and np.max(np.abs(u[0] - g['cfg1_u0'][k])) < TOL_U
+
+
+def test_large_batch_properties(params):
+    """Size-independent properties at BASELINE scale (65536 problems, no oracle): all statuses
+    0, thrusts inside the box, solving twice from the same warm start is deterministic, a
+    solve from the converged SQP point leaves it unchanged (idempotence)."""
+    B, N = 65536, 20
+    ctl, _ = _mk(params, B)
+    rng = np.random.default_rng(11)
+    x0, yref, yref_e = aggressive(rng, B, N, ctl.hover_thrust)
+    u0, st = ctl.solve(x0, yref, yref_e)
+    u0 = u0.copy()
+    assert np.all(st == 0)
+    lo, hi = ctl.input_bounds
+    assert np.all(u0 >= lo - 1e-9) and np.all(u0 <= hi + 1e-9)
+    it = ctl.stats()['qp_iters']
+    assert it.max() <= 40 and it.min() >= 1
+    ctl.invalidate()
+    u1, st1 = ctl.solve(x0, yref, yref_e)
+    assert np.array_equal(u0, u1)          # bit-for-bit repeatable
+    sq, _ = _mk(params, 4096, max_sqp_iter=60, sqp_tol=1e-10)
+    xs, ys, es = x0[:4096], yref[:4096], yref_e[:4096]
+    ua, sa = sq.solve(xs, ys, es)
+    ua = ua.copy()
+    ub, sb = sq.solve(xs, ys, es)          # warm start = fixed point -> no movement
+    ok = (sa == 0) & (sb == 0)
+    assert ok.mean() > 0.9
+    assert np.max(np.abs(ua[ok] - ub[ok])) < 1e-7
