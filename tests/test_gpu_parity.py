@@ -300,8 +300,9 @@ def test_large_batch_properties(params):
     ctl.invalidate()
     u1, st1 = ctl.solve(x0, yref, yref_e)
     assert np.array_equal(u0, u1)          # bit-for-bit repeatable
-    sq, _ = _mk(params, 4096, max_sqp_iter=60, sqp_tol=1e-10)
-    xs, ys, es = x0[:4096], yref[:4096], yref_e[:4096]
+    sq, _ = _mk(params, 4096, max_sqp_iter=80, sqp_tol=1e-9)
+    xs = random_states(rng, 4096)
+    ys, es = setpoint_refs(rng, xs, N, ctl.hover_thrust)
     ua, sa = sq.solve(xs, ys, es)
     ua = ua.copy()
     ub, sb = sq.solve(xs, ys, es)          # warm start = fixed point -> no movement
