@@ -7,10 +7,12 @@ functions here raise ``NmpcError`` / ``OSError`` -- loudly, by design.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 
 _PKG = Path(__file__).resolve().parent
-LIB_PATH = _PKG / 'libnmpc_b200.so'
+# NMPC_B200_LIB points at another build of the SAME library (kernel tuning experiments)
+LIB_PATH = Path(os.environ.get('NMPC_B200_LIB', _PKG / 'libnmpc_b200.so'))
 
 NX, NU, NY = 13, 4, 17
 PRECISION_F64, PRECISION_F32 = 0, 1

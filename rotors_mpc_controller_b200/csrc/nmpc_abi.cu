@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <new>
@@ -194,6 +195,10 @@ static int configure_kernel(nmpc_handle* h, size_t smem) {
   int occ = 0;
   CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, WARPS * 32, smem));
   if (occ < 1) occ = 1;
+  if (const char* cap = getenv("NMPC_B200_MAX_CTAS_PER_SM")) {  // tuning knob (L2 footprint)
+    const int v = atoi(cap);
+    if (v >= 1 && v < occ) occ = v;
+  }
   int grid = h->sm_count * occ;
   const int need = (h->batch + WARPS - 1) / WARPS;
   if (grid > need) grid = need;

@@ -31,7 +31,7 @@ struct WsLayout {
   int M, K, Qi, kff, kffd;
   int xb, q, b, dx, xa;                                            // x-type vectors
   int ub, r, lb, ubd, du, ua, tl, tu, ll, lu, rbl0, rbu0, ru0;    // u-type vectors
-  int dtl, dtu, dll, dlu, Rt, rt, dr;
+  int dtl, dtu, dll, dlu, Rt, rt, dr, itl, itu;
   int total;
 };
 
@@ -75,6 +75,8 @@ __host__ __device__ inline WsLayout make_layout(int N) {
   L.Rt = take(nu);
   L.rt = take(nu);
   L.dr = take(nu);
+  L.itl = take(nu);
+  L.itu = take(nu);
   L.total = o;
   return L;
 }
@@ -100,17 +102,36 @@ __device__ __forceinline__ T warp_sum(T v) {
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
   return v;
 }
-template <typename T>
-__device__ __forceinline__ T warp_min(T v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(FULL, v, o));
-  return v;
+// Min / max over the warp of NON-NEGATIVE, non-NaN values: IEEE bit patterns of such values order
+// like unsigned integers, so two redux.sync (high word, then low word among the winners)
+// replace five shuffle + fmin rounds (a dozen instructions instead of ~70 for FP64).
+__device__ __forceinline__ double warp_min(double v) {
+  const unsigned hi = (unsigned)__double2hiint(v), lo = (unsigned)__double2loint(v);
+  const unsigned mh = __reduce_min_sync(FULL, hi);
+  const unsigned ml = __reduce_min_sync(FULL, hi == mh ? lo : 0xffffffffu);
+  return __hiloint2double((int)mh, (int)ml);
 }
+__device__ __forceinline__ double warp_max(double v) {
+  const unsigned hi = (unsigned)__double2hiint(v), lo = (unsigned)__double2loint(v);
+  const unsigned mh = __reduce_max_sync(FULL, hi);
+  const unsigned ml = __reduce_max_sync(FULL, hi == mh ? lo : 0u);
+  return __hiloint2double((int)mh, (int)ml);
+}
+__device__ __forceinline__ float warp_min(float v) {
+  return __uint_as_float(__reduce_min_sync(FULL, __float_as_uint(v)));
+}
+__device__ __forceinline__ float warp_max(float v) {
+  return __uint_as_float(__reduce_max_sync(FULL, __float_as_uint(v)));
+}
+// Ratio test without a division per candidate: keep the smallest step bound n / (-d) over the
+// candidates with d < 0 as the fraction num / den (den > 0), comparing by cross-multiplication.
 template <typename T>
-__device__ __forceinline__ T warp_max(T v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(FULL, v, o));
-  return v;
+__device__ __forceinline__ void ratio_min(T& num, T& den, T n, T d) {
+  const T dd = -d;
+  if (d < T(0) && n * den < num * dd) {
+    num = n;
+    den = dd;
+  }
 }
 template <typename T>
 __device__ __forceinline__ bool finite_(T v) {
@@ -192,9 +213,10 @@ __device__ __forceinline__ void linearize(const DevCfg<T>& c, T* __restrict__ ws
 #pragma unroll
       for (int i = 0; i < NX; i++) M[(k * NX + i) * NZ + lane] = s[i];
     }
+    T xl = x[0];  // every lane holds the same nominal x; lane i writes component i
 #pragma unroll
-    for (int i = 0; i < NX; i++)
-      if (lane == i) bv[k * NX + i] = x[i] - xb[(k + 1) * NX + i];
+    for (int i = 1; i < NX; i++) xl = (lane == i) ? x[i] : xl;
+    if (lane < NX) bv[k * NX + lane] = xl - xb[(k + 1) * NX + lane];
   }
 }
 
@@ -206,12 +228,12 @@ __device__ __forceinline__ void gradients(const DevCfg<T>& c, T* __restrict__ ws
   const int N = c.N;
   const T* xb = ws + L.xb;
   const T* ub = ws + L.ub;
-  for (int idx = lane; idx < N * NX; idx += 32) {
+  _Pragma("unroll 3") for (int idx = lane; idx < N * NX; idx += 32) {
     const int k = idx / NX, i = idx - k * NX;
     ws[L.q + idx] = c.Wq[i] * (xb[idx] - (T)yref[k * NZ + i]);
   }
   if (lane < NX) ws[L.q + N * NX + lane] = c.We[lane] * (xb[N * NX + lane] - (T)yref_e[lane]);
-  for (int idx = lane; idx < N * NU; idx += 32) {
+  _Pragma("unroll 1") for (int idx = lane; idx < N * NU; idx += 32) {
     const int k = idx >> 2, a = idx & 3;
     const T u = ub[idx];
     ws[L.r + idx] = c.Wr[a] * (u - (T)yref[k * NZ + NX + a]);
@@ -248,12 +270,12 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
   // finite check of the QP data (NaN state / reference -> QP failure, status 4)
   {
     bool fin = true;
-    for (int i = lane; i < nb; i += 32) {
+    _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
       fin = fin && finite_(ws[L.r + i]) && finite_(ws[L.lb + i]) && finite_(ws[L.ubd + i]);
       ws[L.rt + i] = ws[L.r + i];
     }
-    for (int i = lane; i < nxv; i += 32) fin = fin && finite_(ws[L.q + i]);
-    for (int i = lane; i < N * NX; i += 32) fin = fin && finite_(ws[L.b + i]);
+    _Pragma("unroll 3") for (int i = lane; i < nxv; i += 32) fin = fin && finite_(ws[L.q + i]);
+    _Pragma("unroll 3") for (int i = lane; i < N * NX; i += 32) fin = fin && finite_(ws[L.b + i]);
     if (!__all_sync(FULL, fin)) {
       *iters = 0;
       return ST_QPFAIL;
@@ -266,11 +288,11 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
     *iters = it;
     return ST_QPFAIL;
   }
-  forward_sweep<T, false>(c, ws, L, sm, lane, true, L.kff, L.dx, L.du);
+  forward_sweep<T>(c, ws, L, sm, lane, true, false, L.kff, L.dx, L.du);
   // box check + interior-point start
   bool feas = true;
   T res0 = T(0);
-  for (int i = lane; i < nb; i += 32) {
+  _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
     const T du = ws[L.du + i], lb = ws[L.lb + i], ub = ws[L.ubd + i];
     feas = feas && (du >= lb) && (du <= ub);
     const T tl = fmax(du - lb, thr0), tu = fmax(ub - du, thr0);
@@ -295,12 +317,16 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
   const T inv2nb = T(1) / T(2 * nb);
 
   for (; it < c.qp_iter_max; it++) {
-    // complementarity measure + predictor Hessian / gradient
+    // complementarity measure + predictor Hessian / gradient.  The slack reciprocals are
+    // computed once per iteration and reused by the affine and corrector passes.
     T mu = T(0);
-    for (int i = lane; i < nb; i += 32) {
+    _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
       const T tl = ws[L.tl + i], tu = ws[L.tu + i], ll = ws[L.ll + i], lu = ws[L.lu + i];
       mu += tl * ll + tu * lu;
-      const T dl = ll / tl, dw = lu / tu;
+      const T itl = rcp_(tl), itu = rcp_(tu);
+      ws[L.itl + i] = itl;
+      ws[L.itu + i] = itu;
+      const T dl = ll * itl, dw = lu * itu;
       ws[L.Rt + i] = c.Rd[i & 3] + dl + dw;
       ws[L.rt + i] = rho * ws[L.ru0 + i] + dl * (rho * ws[L.rbl0 + i]) + ll -
                      dw * (rho * ws[L.rbu0 + i]) - lu;
@@ -320,28 +346,29 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
       status = ST_QPFAIL;
       break;
     }
-    forward_sweep<T, false>(c, ws, L, sm, lane, false, L.kff, L.xa, L.ua);
-    // affine step length and centering parameter
-    T a_aff = T(1);
-    for (int i = lane; i < nb; i += 32) {
+    forward_sweep<T>(c, ws, L, sm, lane, false, false, L.kff, L.xa, L.ua);
+    // affine step length (division-free ratio test: the running minimum is kept as a fraction
+    // an/ad and candidates are compared by cross-multiplication) and centering parameter
+    T an = T(1), ad = T(1);
+    _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
       const T tl = ws[L.tl + i], tu = ws[L.tu + i], ll = ws[L.ll + i], lu = ws[L.lu + i];
       const T ua = ws[L.ua + i];
       const T dtl = ua + rho * ws[L.rbl0 + i];
       const T dtu = -ua + rho * ws[L.rbu0 + i];
-      const T dll = -(ll / tl) * dtl - ll;
-      const T dlu = -(lu / tu) * dtu - lu;
+      const T dll = -(ll * ws[L.itl + i]) * dtl - ll;
+      const T dlu = -(lu * ws[L.itu + i]) * dtu - lu;
       ws[L.dtl + i] = dtl;
       ws[L.dtu + i] = dtu;
       ws[L.dll + i] = dll;
       ws[L.dlu + i] = dlu;
-      if (dtl < T(0)) a_aff = fmin(a_aff, -tl / dtl);
-      if (dtu < T(0)) a_aff = fmin(a_aff, -tu / dtu);
-      if (dll < T(0)) a_aff = fmin(a_aff, -ll / dll);
-      if (dlu < T(0)) a_aff = fmin(a_aff, -lu / dlu);
+      ratio_min(an, ad, tl, dtl);
+      ratio_min(an, ad, tu, dtu);
+      ratio_min(an, ad, ll, dll);
+      ratio_min(an, ad, lu, dlu);
     }
-    a_aff = warp_min(a_aff);
+    const T a_aff = warp_min(an / ad);
     T mu_aff = T(0);
-    for (int i = lane; i < nb; i += 32) {
+    _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
       mu_aff += (ws[L.tl + i] + a_aff * ws[L.dtl + i]) * (ws[L.ll + i] + a_aff * ws[L.dll + i]) +
                 (ws[L.tu + i] + a_aff * ws[L.dtu + i]) * (ws[L.lu + i] + a_aff * ws[L.dlu + i]);
     }
@@ -351,38 +378,39 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
     const T smu = sigma * mu;
     // weight of the second-order term: min(1, 2 alpha_aff) (breaks Mehrotra 2-cycles)
     const T cw = fmin(T(1), T(2) * a_aff);
-    for (int i = lane; i < nb; i += 32) {
+    _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
       const T sl = smu - cw * ws[L.dtl + i] * ws[L.dll + i];
       const T su = smu - cw * ws[L.dtu + i] * ws[L.dlu + i];
-      ws[L.dr + i] = -sl / ws[L.tl + i] + su / ws[L.tu + i];
+      ws[L.dr + i] = -sl * ws[L.itl + i] + su * ws[L.itu + i];
     }
     __syncwarp();
     // corrector increment (vector-only re-solve), accumulated onto the predictor direction
     delta_backward(c, ws, L, sm, lane);
-    forward_sweep<T, true>(c, ws, L, sm, lane, false, L.kffd, L.xa, L.ua);
-    T alpha = T(1e300);
-    if (sizeof(T) == 4) alpha = T(1e30);
-    for (int i = lane; i < nb; i += 32) {
+    forward_sweep<T>(c, ws, L, sm, lane, false, true, L.kffd, L.xa, L.ua);
+    T bn = T(2), bd = T(1);  // ratios >= 2 cannot bind: alpha = min(1, tau * ratio), tau >= 0.995
+    _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
       const T tl = ws[L.tl + i], tu = ws[L.tu + i], ll = ws[L.ll + i], lu = ws[L.lu + i];
+      const T itl = ws[L.itl + i], itu = ws[L.itu + i];
       const T un = ws[L.ua + i];
       const T sl = smu - cw * ws[L.dtl + i] * ws[L.dll + i];
       const T su = smu - cw * ws[L.dtu + i] * ws[L.dlu + i];
       const T dtl = un + rho * ws[L.rbl0 + i];
       const T dtu = -un + rho * ws[L.rbu0 + i];
-      const T dll = -(ll / tl) * dtl + sl / tl - ll;
-      const T dlu = -(lu / tu) * dtu + su / tu - lu;
+      const T dll = -(ll * itl) * dtl + sl * itl - ll;
+      const T dlu = -(lu * itu) * dtu + su * itu - lu;
       ws[L.dtl + i] = dtl;
       ws[L.dtu + i] = dtu;
       ws[L.dll + i] = dll;
       ws[L.dlu + i] = dlu;
-      if (dtl < T(0)) alpha = fmin(alpha, -tl / dtl);
-      if (dtu < T(0)) alpha = fmin(alpha, -tu / dtu);
-      if (dll < T(0)) alpha = fmin(alpha, -ll / dll);
-      if (dlu < T(0)) alpha = fmin(alpha, -lu / dlu);
+      ratio_min(bn, bd, tl, dtl);
+      ratio_min(bn, bd, tu, dtu);
+      ratio_min(bn, bd, ll, dll);
+      ratio_min(bn, bd, lu, dlu);
     }
+    T alpha = bn / bd;
     // NaN anywhere must surface: fmin drops NaNs, so test the directions explicitly
     bool fin = true;
-    for (int i = lane; i < nb; i += 32)
+    _Pragma("unroll 1") for (int i = lane; i < nb; i += 32)
       fin = fin && finite_(ws[L.dtl + i]) && finite_(ws[L.dll + i]) && finite_(ws[L.dlu + i]);
     if (!__all_sync(FULL, fin)) {
       status = ST_QPFAIL;
@@ -395,14 +423,14 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
       status = ST_MINSTEP;
       break;
     }
-    for (int i = lane; i < nb; i += 32) {
+    _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
       ws[L.du + i] += alpha * ws[L.ua + i];
       ws[L.tl + i] += alpha * ws[L.dtl + i];
       ws[L.tu + i] += alpha * ws[L.dtu + i];
       ws[L.ll + i] += alpha * ws[L.dll + i];
       ws[L.lu + i] += alpha * ws[L.dlu + i];
     }
-    for (int i = lane; i < nxv; i += 32) ws[L.dx + i] += alpha * ws[L.xa + i];
+    _Pragma("unroll 3") for (int i = lane; i < nxv; i += 32) ws[L.dx + i] += alpha * ws[L.xa + i];
     rho *= (T(1) - alpha);
     __syncwarp();
   }
@@ -453,11 +481,11 @@ __device__ __forceinline__ void solve_one(const SolveArgs<T>& A, const WsLayout&
   // warm start (controller.py:416-431): previous solution un-shifted with stage-0 x <- x0,
   // or (x0, u = 0) on every stage when the previous solve is not valid.
   const bool warm = A.valid[prob] != 0;
-  for (int i = lane; i < nxv; i += 32) {
+  _Pragma("unroll 3") for (int i = lane; i < nxv; i += 32) {
     const int ii = i % NX;
     ws[L.xb + i] = (T)((warm && i >= NX) ? xtraj[i] : x0[ii]);
   }
-  for (int i = lane; i < nuv; i += 32) ws[L.ub + i] = warm ? (T)utraj[i] : T(0);
+  _Pragma("unroll 1") for (int i = lane; i < nuv; i += 32) ws[L.ub + i] = warm ? (T)utraj[i] : T(0);
   __syncwarp();
 
   int status = ST_SUCCESS;
@@ -480,14 +508,14 @@ __device__ __forceinline__ void solve_one(const SolveArgs<T>& A, const WsLayout&
     __syncwarp();
     T step = T(0);
     bool fin = true;
-    for (int i = lane; i < nxv; i += 32) {
+    _Pragma("unroll 3") for (int i = lane; i < nxv; i += 32) {
       const T d = ws[L.dx + i];
       const T v = ws[L.xb + i] + d;  // full step
       ws[L.xb + i] = v;
       step = fmax(step, fabs(d));
       fin = fin && finite_(v);
     }
-    for (int i = lane; i < nuv; i += 32) {
+    _Pragma("unroll 1") for (int i = lane; i < nuv; i += 32) {
       const T d = ws[L.du + i];
       const T v = ws[L.ub + i] + d;
       ws[L.ub + i] = v;
@@ -509,8 +537,8 @@ __device__ __forceinline__ void solve_one(const SolveArgs<T>& A, const WsLayout&
 
   // K3 epilogue: outputs, warm-start store, command mapping with last-valid fallback
   if (status == ST_SUCCESS) {
-    for (int i = lane; i < nxv; i += 32) xtraj[i] = (double)ws[L.xb + i];
-    for (int i = lane; i < nuv; i += 32) utraj[i] = (double)ws[L.ub + i];
+    _Pragma("unroll 3") for (int i = lane; i < nxv; i += 32) xtraj[i] = (double)ws[L.xb + i];
+    _Pragma("unroll 1") for (int i = lane; i < nuv; i += 32) utraj[i] = (double)ws[L.ub + i];
   }
   if (lane < NU) {
     const T u = (status == ST_SUCCESS) ? ws[L.ub + lane] : T(0);

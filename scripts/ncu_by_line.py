@@ -94,12 +94,13 @@ def bucket(ch):
         if fr[0] == 'nmpc_model.cuh':
             return 'model'
     return 'ipm/sqp elementwise + other'
-bs, be = collections.Counter(), collections.Counter()
+bs, be, bn = collections.Counter(), collections.Counter(), collections.Counter()
 for r, ch in zip(body[:n], chains[:n]):
     b = bucket(ch)
     bs[b] += int(r[isamp])
     be[b] += int(r[iexec])
-print('--- buckets (samples %, executed warp-instructions %)')
+    bn[b] += 1
+print('--- buckets (samples %, executed warp-instructions %, static SASS instructions)')
 te = sum(be.values())
 for b, s in bs.most_common():
-    print(f'  {b:32s} {100.0 * s / tot:5.1f}%  {100.0 * be[b] / te:5.1f}%')
+    print(f'  {b:32s} {100.0 * s / tot:5.1f}%  {100.0 * be[b] / te:5.1f}%  {bn[b]:6d}')

@@ -309,3 +309,30 @@ def test_large_batch_properties(params):
     ok = (sa == 0) & (sb == 0)
     assert ok.mean() > 0.9
     assert np.max(np.abs(ua[ok] - ub[ok])) < 1e-7
+
+
+@pytest.mark.parametrize('kind', ['cfg2', 'aggressive'])
+def test_fp32_variant(params, O, kind):
+    """FP32 compute variant (north_star: u0 within 1e-3 relative of the FP64 reference; measured
+    against the FP64 oracle with the thrust scale max(|u0|, hover) as denominator), identical
+    status codes.  I/O stays FP64."""
+    B, N = 512, 20
+    ctl, p = _mk(params, B, precision='f32')
+    rng = np.random.default_rng(21)
+    if kind == 'cfg2':
+        x0 = random_states(rng, B)
+        yref, yref_e = setpoint_refs(rng, x0, N, ctl.hover_thrust)
+    else:
+        x0, yref, yref_e = aggressive(rng, B, N, ctl.hover_thrust)
+    u0, st = ctl.solve(x0, yref, yref_e)
+    ob = O.OracleBatch(O.config_from_params(params), B)
+    ur, sr, _, _ = ob.solve(x0, yref, yref_e)
+    assert np.array_equal(st, sr)
+    rel = np.abs(u0 - ur) / np.maximum(np.abs(ur), ctl.hover_thrust)
+    assert rel.max() < 1e-3, rel.max()
+    # warm-started second solve stays inside the tolerance as well
+    u1, st1 = ctl.solve(x0, yref, yref_e)
+    ur1, sr1, _, _ = ob.solve(x0, yref, yref_e)
+    assert np.array_equal(st1, sr1)
+    rel1 = np.abs(u1 - ur1) / np.maximum(np.abs(ur1), ctl.hover_thrust)
+    assert rel1.max() < 1e-3, rel1.max()
