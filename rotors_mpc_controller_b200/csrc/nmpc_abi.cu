@@ -141,7 +141,7 @@ DevCfg<T> make_devcfg(const nmpc_config_t& c) {
   d.hover = (T)(c.mass * c.gravity / 4.0);
   d.sqp_tol = (T)c.sqp_tol;
   double tol = c.ipm_tol;
-  if (sizeof(T) == 4 && tol < 1e-6) tol = 1e-6;  // FP32 cannot resolve a tighter complementarity
+  if (sizeof(T) == 4 && tol < 1e-9) tol = 1e-9;  // FP32: slack*multiplier products resolve to ~1e-9
   d.ipm_tol = (T)tol;
   return d;
 }

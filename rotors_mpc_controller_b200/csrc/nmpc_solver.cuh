@@ -343,7 +343,9 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
     __syncwarp();
     ok = factor_sweep(c, ws, L, sm, lane, false);
     if (!ok) {
-      status = ST_QPFAIL;
+      // FP32 precision floor: once the complementarity is below 1e-6 a lost pivot means the
+      // barrier Hessian can no longer be resolved in single precision -> keep the iterate
+      status = (sizeof(T) == 4 && mu <= T(1e-6)) ? ST_SUCCESS : ST_QPFAIL;
       break;
     }
     forward_sweep<T>(c, ws, L, sm, lane, false, false, L.kff, L.xa, L.ua);
