@@ -129,6 +129,79 @@ int nmpc_set_trajectories(nmpc_handle_t *h, const double *xtraj, const double *u
 int nmpc_discretize_device(nmpc_handle_t *h, int32_t n, const double *x, const double *u,
                            double *xn, double *A, double *B, void *stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Closed loop on the device: everything a Monte-Carlo run needs
+ * around the solve, so that states, references and commands never leave HBM.  All pointers are
+ * DEVICE pointers, all calls asynchronous on `stream`.
+ * ------------------------------------------------------------------------------------------- */
+
+/* ReferenceGenerator.build_horizon (reference.py:75-91) + update_hover_thrust (:70-72) stacked as
+ * controller.py:433-445 does, for every problem: pos[batch,3], yaw[batch] (NULL = 0) ->
+ * yref[batch,N,17], yref_e[batch,13]. */
+int nmpc_reference_setpoint_device(nmpc_handle_t *h, const double *pos, const double *yaw,
+                                   double *yref, double *yref_e, void *stream);
+/* Figure-8 track p(t) = c + (A sin wt, A/2 sin 2wt, 0), w = 2 pi / period, sampled (with its
+ * velocity) at t0[b] + t_offset + k dt, k = 0..N. */
+int nmpc_reference_figure8_device(nmpc_handle_t *h, const double *t0, const double *amplitude,
+                                  const double *period, const double centre[3], double t_offset,
+                                  double *yref, double *yref_e, void *stream);
+
+/* nav_msgs/Odometry -> solver state exactly as nodes/mpc_controller_node:88-113 does (euler
+ * angles :25-44, R(rpy) v_body :139-150, xyzw -> wxyz) followed by the quaternion normalisation of
+ * controller.py:406-411.  odom[batch,13] = [p(3), q_xyzw(4), v_body(3), w(3)] -> x0[batch,13];
+ * zero_quat[batch] (may be NULL) flags the inputs for which controller.py:407-408 raises. */
+int nmpc_odometry_to_state_device(nmpc_handle_t *h, const double *odom, double *x0,
+                                  int32_t *zero_quat, void *stream);
+
+/* Plant used by closed-loop runs (RK4 of the controller model, controller.py:286-346). */
+typedef struct nmpc_plant {
+  int32_t substeps;    /* RK4 sub-steps per control interval (>= 1) */
+  int32_t motor_model; /* 0: thrust = clipped command; 1: first-order rotor-speed lag
+                          (rotors_gazebo_plugins common.h:147-183), thrust = kf w^2 */
+  double dt;           /* control interval */
+  double tau_up;       /* rotor time constants (hummingbird.xacro: 0.0125 / 0.025 s) */
+  double tau_down;
+  double rotor_drag;   /* rotor_drag_coefficient (gazebo_motor_model.cpp:443-453), 0 = off */
+  double mass;         /* plant mass; <= 0 means the controller's */
+} nmpc_plant_t;
+
+/* One control interval for every problem: x[batch,13] (in/out, quaternion left as integrated),
+ * x0[batch,13] (out, may be NULL: the state with the quaternion normalised, i.e. what solve()
+ * is fed), thrust[batch,4] (clipped command; NULL = zero), rotor_speed[batch,4] (in/out, only for
+ * motor_model 1).  With substeps = 0 only x0 is produced. */
+int nmpc_plant_step_device(nmpc_handle_t *h, const nmpc_plant_t *plant, double *x, double *x0,
+                           const double *thrust, double *rotor_speed, void *stream);
+
+#define NMPC_REF_SETPOINT 0
+#define NMPC_REF_FIGURE8 1
+#define NMPC_NSTATS 8
+/* Whole closed-loop run: `steps` times (reference -> solve with warm start -> command with
+ * last-valid fallback -> plant step -> statistics).  2 or 3 kernel launches per step, no host
+ * synchronisation inside.  stats[batch,8] (device, zeroed by the caller) accumulates per
+ * problem: 0 sum |p-p_ref|^2, 1 last |p-p_ref|, 2 #solves with status != 0, 3 sum of Riccati
+ * factorisations, 4 #steps with a rotor at a thrust bound, 5 max |p-p_ref|, 6 sum of thrusts,
+ * 7 #non-finite states. */
+typedef struct nmpc_rollout {
+  int32_t steps;
+  int32_t ref_mode;        /* NMPC_REF_SETPOINT | NMPC_REF_FIGURE8 */
+  nmpc_plant_t plant;
+  double *x;               /* [batch,13] plant state, in/out */
+  double *rotor_speed;     /* [batch,4] in/out (motor_model 1) or NULL */
+  const double *sp_pos;    /* set-point mode: [batch,3] */
+  const double *sp_yaw;    /* [batch] or NULL */
+  const double *f8_t0;     /* figure-8 mode: [batch] each */
+  const double *f8_amplitude;
+  const double *f8_period;
+  double f8_centre[3];
+  double t_start;          /* time of the first control step (figure-8 phase) */
+  double *stats;           /* [batch,8] or NULL */
+} nmpc_rollout_t;
+int nmpc_rollout_device(nmpc_handle_t *h, const nmpc_rollout_t *run, void *stream);
+/* Outputs of the last solve made by nmpc_rollout_device / nmpc_solve_host (device pointers owned
+ * by the handle): u0[batch,4], status[batch], thrust[batch,4], speed[batch,4]. */
+int nmpc_last_outputs(nmpc_handle_t *h, const double **u0, const int32_t **status,
+                      const double **thrust, const double **speed);
+
 /* Measured DFMA throughput of `device` in TFLOP/s (8 independent FMA chains per thread,
  * best of 4): the FP64 roofline denominator used by bench.py. */
 int nmpc_fp64_peak(int32_t device, double *tflops);

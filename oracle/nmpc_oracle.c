@@ -219,3 +219,57 @@ void orc_plant_step(const orc_config *c, const double *x, const double *u, doubl
   }
   memcpy(xn, xc, sizeof(xc));
 }
+
+/* Plant with the optional RotorS motor model: first-order rotor-speed filter
+ * (third_party/rotors_simulator/rotors_gazebo_plugins/include/rotors_gazebo_plugins/common.h:147-183,
+ * applied once per integration step like gazebo_motor_model.cpp:476-477, thrust = kf w^2 from the
+ * speed BEFORE the filter update, :432-434) and rotor drag -sum|w_i| c_drag v_perp (:443-453).
+ * rotor[4] is in/out when motor_model = 1.  mass <= 0 selects the controller's mass. */
+void orc_plant_step_ext(const orc_config *c, const double *x, const double *u, double dt,
+                        int substeps, int motor_model, double tau_up, double tau_down,
+                        double rotor_drag, double mass, double *rotor, double *xn) {
+  orc_config cp = *c;
+  if (mass > 0.0) cp.mass = mass;
+  double xc[NX], w[NU], wcmd[NU];
+  memcpy(xc, x, sizeof(xc));
+  const double h = dt / (double)(substeps > 0 ? substeps : 1);
+  const double kf = c->kf > 1e-9 ? c->kf : 1e-9;
+  for (int i = 0; i < NU; i++) {
+    wcmd[i] = sqrt((u[i] > 0.0 ? u[i] : 0.0) / kf);
+    w[i] = motor_model ? rotor[i] : wcmd[i];
+  }
+  const double a_up = motor_model ? exp(-h / tau_up) : 0.0;
+  const double a_dn = motor_model ? exp(-h / tau_down) : 0.0;
+  for (int s = 0; s < substeps; s++) {
+    double ua[NU], saw = 0.0;
+    for (int i = 0; i < NU; i++) {
+      ua[i] = motor_model ? c->kf * w[i] * w[i] : u[i];
+      saw += fabs(w[i]);
+    }
+    double k[4][NX], t[NX];
+    for (int st = 0; st < 4; st++) {
+      const double a = (st == 0) ? 0.0 : (st == 3 ? 1.0 : 0.5);
+      for (int i = 0; i < NX; i++) t[i] = (st == 0) ? xc[i] : xc[i] + a * h * k[st - 1][i];
+      orc_f(&cp, t, ua, k[st]);
+      if (rotor_drag != 0.0) {
+        const double qw = t[6], qx = t[7], qy = t[8], qz = t[9];
+        const double zx = 2.0 * (qx * qz + qw * qy), zy = 2.0 * (qy * qz - qw * qx),
+                     zz = 1.0 - 2.0 * (qx * qx + qy * qy);
+        const double vz = t[3] * zx + t[4] * zy + t[5] * zz;
+        const double kd = saw * rotor_drag * (1.0 / cp.mass);
+        k[st][3] -= kd * (t[3] - vz * zx);
+        k[st][4] -= kd * (t[4] - vz * zy);
+        k[st][5] -= kd * (t[5] - vz * zz);
+      }
+    }
+    for (int i = 0; i < NX; i++)
+      xc[i] += h / 6.0 * (k[0][i] + 2.0 * k[1][i] + 2.0 * k[2][i] + k[3][i]);
+    if (motor_model)
+      for (int i = 0; i < NU; i++) {
+        const double a = (wcmd[i] > w[i]) ? a_up : a_dn;
+        w[i] = a * w[i] + (1.0 - a) * wcmd[i];
+      }
+  }
+  memcpy(xn, xc, sizeof(xc));
+  if (motor_model) memcpy(rotor, w, sizeof(w));
+}

@@ -122,6 +122,11 @@ void orc_solve_batch(const orc_config *c, int batch, const double *x0, const dou
 void orc_plant_step(const orc_config *c, const double *x, const double *u, double dt,
                     int substeps, double *xn);
 
+/* Plant with the optional RotorS first-order motor lag + rotor drag (see nmpc_oracle.c). */
+void orc_plant_step_ext(const orc_config *c, const double *x, const double *u, double dt,
+                        int substeps, int motor_model, double tau_up, double tau_down,
+                        double rotor_drag, double mass, double *rotor, double *xn);
+
 #ifdef __cplusplus
 }
 #endif

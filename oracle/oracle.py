@@ -11,6 +11,7 @@ see ``oracle/nmpc_oracle.h``.  Only ``tests/``, ``__graft_entry__.smoke()`` and
 from __future__ import annotations
 
 import ctypes as C
+import math
 import os
 import subprocess
 from pathlib import Path
@@ -253,3 +254,130 @@ class OraclePositionNMPC:
         yref, yref_e = stack_reference(reference, self.cfg.N)
         u0, status, _, _ = self._batch.solve(x0[None], yref[None], yref_e[None])
         return u0[0].copy(), int(status[0])
+
+
+# ------------------------------------------------------------------ closed loop (f1-f3 checkers)
+def plant_step_ext(cfg, x, u, dt, substeps=1, motor_model=0, tau_up=0.0125, tau_down=0.025,
+                   rotor_drag=0.0, mass=0.0, rotor=None):
+    """orc_plant_step_ext: returns (xn, rotor_speed_new)."""
+    xn = np.zeros(NX)
+    rot = np.zeros(NU) if rotor is None else np.ascontiguousarray(rotor, float).copy()
+    lib().orc_plant_step_ext.restype = None
+    lib().orc_plant_step_ext(C.byref(cfg), _p(np.ascontiguousarray(x, float)),
+                             _p(np.ascontiguousarray(u, float)), C.c_double(dt),
+                             C.c_int(substeps), C.c_int(motor_model), C.c_double(tau_up),
+                             C.c_double(tau_down), C.c_double(rotor_drag), C.c_double(mass),
+                             _p(rot), _p(xn))
+    return xn, rot
+
+
+def setpoint_reference(cfg, positions, yaws=None):
+    """B x (ReferenceGenerator.build_horizon, reference.py:75-91, with update_hover_thrust :70-72)
+    stacked as controller.py:433-445."""
+    p = np.asarray(positions, float).reshape(-1, 3)
+    B, N = p.shape[0], cfg.N
+    yaw = np.zeros(B) if yaws is None else np.asarray(yaws, float).reshape(B)
+    hover = cfg.mass * cfg.gravity / 4.0
+    yref, yref_e = np.zeros((B, N, NZ)), np.zeros((B, NX))
+    for b in range(B):
+        half = 0.5 * yaw[b]                       # reference.py:11-13
+        q = np.array([math.cos(half), 0.0, 0.0, math.sin(half)])
+        row = np.concatenate([p[b], np.zeros(3), q, np.zeros(3)])
+        yref[b, :, :NX] = row
+        yref[b, :, NX:] = hover
+        yref_e[b] = row
+    return yref, yref_e
+
+
+def figure8_reference(cfg, t0, amplitude, period, centre=(0.0, 0.0, 1.5), t_offset=0.0):
+    """p(t) = c + (A sin wt, A/2 sin 2wt, 0) and its velocity at t0 + t_offset + k dt."""
+    t0 = np.asarray(t0, float).reshape(-1)
+    B, N = t0.shape[0], cfg.N
+    A = np.broadcast_to(np.asarray(amplitude, float), (B,))
+    per = np.broadcast_to(np.asarray(period, float), (B,))
+    hover = cfg.mass * cfg.gravity / 4.0
+    yref, yref_e = np.zeros((B, N, NZ)), np.zeros((B, NX))
+    for b in range(B):
+        w = 2.0 * math.pi / per[b]
+        for k in range(N + 1):
+            wt = w * (t0[b] + t_offset + cfg.dt * k)
+            row = np.zeros(NX)
+            row[0] = centre[0] + A[b] * math.sin(wt)
+            row[1] = centre[1] + 0.5 * A[b] * math.sin(2.0 * wt)
+            row[2] = centre[2]
+            row[3] = A[b] * w * math.cos(wt)
+            row[4] = A[b] * w * math.cos(2.0 * wt)
+            row[6] = 1.0
+            if k < N:
+                yref[b, k, :NX] = row
+                yref[b, k, NX:] = hover
+            else:
+                yref_e[b] = row
+    return yref, yref_e
+
+
+def odometry_to_state(odom):
+    """nodes/mpc_controller_node:88-113 (+ quaternion_to_euler :25-44, _rotation_matrix :139-150)
+    followed by controller.py:401-411.  odom = [p(3), q_xyzw(4), v_body(3), w(3)].
+    Returns (x0[13], zero_quaternion flag)."""
+    o = np.asarray(odom, float).reshape(13)
+    qx, qy, qz, qw = o[3], o[4], o[5], o[6]
+    norm = math.sqrt(qx * qx + qy * qy + qz * qz + qw * qw)
+    if norm == 0.0:
+        roll = pitch = yaw = 0.0
+    else:
+        ex, ey, ez, ew = qx / norm, qy / norm, qz / norm, qw / norm
+        roll = math.atan2(2.0 * (ew * ex + ey * ez), 1.0 - 2.0 * (ex * ex + ey * ey))
+        sinp = 2.0 * (ew * ey - ez * ex)
+        pitch = math.copysign(math.pi / 2.0, sinp) if abs(sinp) >= 1.0 else math.asin(sinp)
+        yaw = math.atan2(2.0 * (ew * ez + ex * ey), 1.0 - 2.0 * (ey * ey + ez * ez))
+    cr, sr, cp, sp = math.cos(roll), math.sin(roll), math.cos(pitch), math.sin(pitch)
+    cy, sy = math.cos(yaw), math.sin(yaw)
+    rot = np.array([[cp * cy, cy * sp * sr - sy * cr, cy * sp * cr + sy * sr],
+                    [cp * sy, sy * sp * sr + cy * cr, sy * sp * cr - cy * sr],
+                    [-sp, cp * sr, cp * cr]])
+    q = np.array([qw, qx, qy, qz])
+    nq = np.linalg.norm(q)
+    x0 = np.concatenate([o[0:3], rot @ o[7:10], q / nq if nq != 0.0 else q, o[10:13]])
+    return x0, nq == 0.0
+
+
+def closed_loop(cfg, x_init, steps, ref_fn, pref_fn, plant=None, rotor_init=None):
+    """Reference closed loop for a batch: per step reference -> orc_solve_batch (warm start,
+    command map, last-valid fallback) -> plant step -> statistics, exactly the order of
+    nmpc_rollout_device.  ref_fn(k) -> (yref, yref_e); pref_fn(k) -> p_ref[B,3] the error of the
+    NEW state is measured against.  Returns (x, stats[B,8], rotor, last outputs)."""
+    plant = {**dict(dt=cfg.dt, substeps=1, motor_model=0, tau_up=0.0125, tau_down=0.025,
+                    rotor_drag=0.0, mass=0.0), **(plant or {})}
+    x = np.array(x_init, float).reshape(-1, NX).copy()
+    B = x.shape[0]
+    ob = OracleBatch(cfg, B)
+    rotor = np.zeros((B, NU)) if rotor_init is None else np.array(rotor_init, float).copy()
+    stats = np.zeros((B, 8))
+    out = None
+    for k in range(steps):
+        yref, yref_e = ref_fn(k)
+        x0 = x.copy()
+        nq = np.linalg.norm(x0[:, 6:10], axis=1)
+        x0[:, 6:10] = x0[:, 6:10] / np.where(nq != 0.0, nq, 1.0)[:, None]
+        u0, status, thrust, speed = ob.solve(x0, yref, yref_e)
+        out = (u0, status, thrust, speed)
+        pref = pref_fn(k)
+        for b in range(B):
+            x[b], rot = plant_step_ext(cfg, x[b], thrust[b], plant['dt'], plant['substeps'],
+                                       plant['motor_model'], plant['tau_up'], plant['tau_down'],
+                                       plant['rotor_drag'], plant['mass'], rotor[b])
+            if plant['motor_model']:
+                rotor[b] = rot
+        e = np.linalg.norm(x[:, 0:3] - pref, axis=1)
+        stats[:, 0] += e * e
+        stats[:, 1] = e
+        stats[:, 2] += (status != 0)
+        stats[:, 3] += ob.qp_iters
+        lo, hi = np.array(cfg.lbu[:]), np.array(cfg.ubu[:])
+        tol = 1e-9 * (hi - lo)
+        stats[:, 4] += np.any((thrust <= lo + tol) | (thrust >= hi - tol), axis=1)
+        stats[:, 5] = np.maximum(stats[:, 5], e)
+        stats[:, 6] += thrust.sum(axis=1)
+        stats[:, 7] += ~np.all(np.isfinite(x), axis=1)
+    return x, stats, rotor, out

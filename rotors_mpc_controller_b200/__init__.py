@@ -1,5 +1,6 @@
 """rotors_mpc_controller_b200 -- B200-native drop-in for the acados-backed NMPC of
 Anaskherro/rotors_mpc_controller (same exports as the reference's ``__init__.py:3-12``)."""
+from .closed_loop import ClosedLoop, Plant
 from .controller import BatchedPositionNMPC, ControllerParams, PositionNMPC
 from .params import apply_dynamic_configuration, load_params
 from .reference import BatchReference, ReferenceGenerator, stack_reference
@@ -7,6 +8,8 @@ from .reference import BatchReference, ReferenceGenerator, stack_reference
 __all__ = [
     'PositionNMPC',
     'BatchedPositionNMPC',
+    'ClosedLoop',
+    'Plant',
     'ControllerParams',
     'ReferenceGenerator',
     'BatchReference',

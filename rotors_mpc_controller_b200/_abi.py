@@ -42,6 +42,24 @@ class NmpcConfig(C.Structure):
     ]
 
 
+class NmpcPlant(C.Structure):
+    """Mirror of ``nmpc_plant_t``."""
+    _fields_ = [('substeps', C.c_int32), ('motor_model', C.c_int32), ('dt', C.c_double),
+                ('tau_up', C.c_double), ('tau_down', C.c_double), ('rotor_drag', C.c_double),
+                ('mass', C.c_double)]
+
+
+class NmpcRollout(C.Structure):
+    """Mirror of ``nmpc_rollout_t`` (all pointers are device addresses)."""
+    _fields_ = [('steps', C.c_int32), ('ref_mode', C.c_int32), ('plant', NmpcPlant),
+                ('x', C.c_void_p), ('rotor_speed', C.c_void_p), ('sp_pos', C.c_void_p),
+                ('sp_yaw', C.c_void_p), ('f8_t0', C.c_void_p), ('f8_amplitude', C.c_void_p),
+                ('f8_period', C.c_void_p), ('f8_centre', C.c_double * 3),
+                ('t_start', C.c_double), ('stats', C.c_void_p)]
+
+
+REF_SETPOINT, REF_FIGURE8, NSTATS = 0, 1, 8
+
 # every symbol include/nmpc_b200.h declares: (restype, argtypes)
 _vp, _dp, _ip, _bp = C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p
 SYMBOLS = {
@@ -57,6 +75,14 @@ SYMBOLS = {
     'nmpc_get_stats': (C.c_int, [_vp, _ip, _ip, C.c_int32]),
     'nmpc_set_trajectories': (C.c_int, [_vp, _dp, _dp, _bp]),
     'nmpc_discretize_device': (C.c_int, [_vp, C.c_int32, _dp, _dp, _dp, _dp, _dp, _vp]),
+    'nmpc_reference_setpoint_device': (C.c_int, [_vp, _dp, _dp, _dp, _dp, _vp]),
+    'nmpc_reference_figure8_device': (C.c_int, [_vp, _dp, _dp, _dp, C.POINTER(C.c_double),
+                                                C.c_double, _dp, _dp, _vp]),
+    'nmpc_odometry_to_state_device': (C.c_int, [_vp, _dp, _dp, _ip, _vp]),
+    'nmpc_plant_step_device': (C.c_int, [_vp, C.POINTER(NmpcPlant), _dp, _dp, _dp, _dp, _vp]),
+    'nmpc_rollout_device': (C.c_int, [_vp, C.POINTER(NmpcRollout), _vp]),
+    'nmpc_last_outputs': (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp),
+                                    C.POINTER(_vp)]),
     'nmpc_fp64_peak': (C.c_int, [C.c_int32, C.POINTER(C.c_double)]),
     'nmpc_batch': (C.c_int, [_vp]),
     'nmpc_horizon': (C.c_int, [_vp]),

@@ -10,6 +10,7 @@
 
 #include "../../include/nmpc_b200.h"
 #include "nmpc_solver.cuh"
+#include "nmpc_closedloop.cuh"
 
 using namespace nmpc;
 
@@ -500,6 +501,154 @@ int nmpc_discretize_device(nmpc_handle_t* h, int32_t n, const double* x, const d
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (h->cfg.precision == NMPC_PRECISION_F64) return launch_disc<double>(h, n, x, u, xn, A, B, st);
   return launch_disc<float>(h, n, x, u, xn, A, B, st);
+}
+
+
+// ------------------------------------------------------------------ closed loop (f1-f3)
+static PlantCfg make_plantcfg(const nmpc_handle* h, const nmpc_plant_t& p) {
+  PlantCfg pc;
+  pc.substeps = p.substeps;
+  pc.motor_model = p.motor_model;
+  pc.dt = p.dt;
+  pc.tau_up = p.tau_up;
+  pc.tau_down = p.tau_down;
+  pc.rotor_drag = p.rotor_drag;
+  pc.inv_mass = 1.0 / (p.mass > 0.0 ? p.mass : h->cfg.mass);
+  return pc;
+}
+
+static int validate_plant(const nmpc_plant_t* p, const double* rotor_speed) {
+  if (!p || p->substeps < 0 || p->substeps > 100000) return NMPC_E_INVALID;
+  if (p->substeps > 0 && !(p->dt > 0.0)) return NMPC_E_INVALID;
+  if (p->motor_model != 0 && p->motor_model != 1) return NMPC_E_INVALID;
+  if (p->motor_model == 1 && (!rotor_speed || !(p->tau_up > 0.0) || !(p->tau_down > 0.0)))
+    return NMPC_E_INVALID;
+  return NMPC_OK;
+}
+
+int nmpc_reference_setpoint_device(nmpc_handle_t* h, const double* pos, const double* yaw,
+                                   double* yref, double* yref_e, void* stream) {
+  if (!h || !pos || !yref || !yref_e) return NMPC_E_INVALID;
+  CK(cudaSetDevice(h->device));
+  const int N = h->cfg.N;
+  const size_t total = (size_t)h->batch * ((size_t)N * NZ + NX);
+  size_t grid = (total + 255) / 256;
+  if (grid > (size_t)h->sm_count * 16) grid = (size_t)h->sm_count * 16;
+  const double hover = h->cfg.mass * h->cfg.gravity / 4.0;
+  reference_setpoint_kernel<<<(unsigned)grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      h->batch, N, pos, yaw, hover, yref, yref_e);
+  h->launches++;
+  CK(cudaGetLastError());
+  return NMPC_OK;
+}
+
+int nmpc_reference_figure8_device(nmpc_handle_t* h, const double* t0, const double* amplitude,
+                                  const double* period, const double centre[3], double t_offset,
+                                  double* yref, double* yref_e, void* stream) {
+  if (!h || !t0 || !amplitude || !period || !centre || !yref || !yref_e) return NMPC_E_INVALID;
+  CK(cudaSetDevice(h->device));
+  const int N = h->cfg.N;
+  const size_t total = (size_t)h->batch * (N + 1);
+  size_t grid = (total + 127) / 128;
+  if (grid > (size_t)h->sm_count * 32) grid = (size_t)h->sm_count * 32;
+  const double hover = h->cfg.mass * h->cfg.gravity / 4.0;
+  reference_figure8_kernel<<<(unsigned)grid, 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      h->batch, N, h->cfg.dt, t_offset, t0, amplitude, period, centre[0], centre[1], centre[2],
+      hover, yref, yref_e);
+  h->launches++;
+  CK(cudaGetLastError());
+  return NMPC_OK;
+}
+
+int nmpc_odometry_to_state_device(nmpc_handle_t* h, const double* odom, double* x0,
+                                  int32_t* zero_quat, void* stream) {
+  if (!h || !odom || !x0) return NMPC_E_INVALID;
+  CK(cudaSetDevice(h->device));
+  odometry_to_state_kernel<<<(h->batch + 127) / 128, 128, 0,
+                             reinterpret_cast<cudaStream_t>(stream)>>>(h->batch, odom, x0,
+                                                                       zero_quat);
+  h->launches++;
+  CK(cudaGetLastError());
+  return NMPC_OK;
+}
+
+static int launch_plant(nmpc_handle* h, const nmpc_plant_t* plant, double* x, double* x0,
+                        const double* thrust, double* rotor_speed, const double* pref,
+                        size_t pref_stride, const int32_t* status, const int32_t* qp_iters,
+                        double* stats, cudaStream_t st) {
+  const DevCfg<double> c = make_devcfg<double>(h->cfg);
+  const PlantCfg pc = make_plantcfg(h, *plant);
+  plant_step_kernel<<<(h->batch + 127) / 128, 128, 0, st>>>(c, pc, h->batch, x, x0, thrust,
+                                                            rotor_speed, pref, pref_stride, status,
+                                                            qp_iters, stats);
+  h->launches++;
+  CK(cudaGetLastError());
+  return NMPC_OK;
+}
+
+int nmpc_plant_step_device(nmpc_handle_t* h, const nmpc_plant_t* plant, double* x, double* x0,
+                           const double* thrust, double* rotor_speed, void* stream) {
+  if (!h || !x) return NMPC_E_INVALID;
+  int rc = validate_plant(plant, rotor_speed);
+  if (rc != NMPC_OK) return rc;
+  CK(cudaSetDevice(h->device));
+  return launch_plant(h, plant, x, x0, thrust, rotor_speed, nullptr, 0, nullptr, nullptr, nullptr,
+                      reinterpret_cast<cudaStream_t>(stream));
+}
+
+int nmpc_rollout_device(nmpc_handle_t* h, const nmpc_rollout_t* run, void* stream) {
+  if (!h || !run || !run->x || run->steps < 0) return NMPC_E_INVALID;
+  int rc = validate_plant(&run->plant, run->rotor_speed);
+  if (rc != NMPC_OK || run->plant.substeps < 1) return NMPC_E_INVALID;
+  if (run->ref_mode == NMPC_REF_SETPOINT) {
+    if (!run->sp_pos) return NMPC_E_INVALID;
+  } else if (run->ref_mode == NMPC_REF_FIGURE8) {
+    if (!run->f8_t0 || !run->f8_amplitude || !run->f8_period) return NMPC_E_INVALID;
+  } else {
+    return NMPC_E_INVALID;
+  }
+  CK(cudaSetDevice(h->device));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const int N = h->cfg.N;
+  // state handed to the first solve: normalised copy of the plant state (substeps = 0)
+  nmpc_plant_t norm_only = run->plant;
+  norm_only.substeps = 0;
+  rc = launch_plant(h, &norm_only, run->x, h->s_x0, nullptr, run->rotor_speed, nullptr, 0, nullptr,
+                    nullptr, nullptr, st);
+  if (rc != NMPC_OK) return rc;
+  if (run->ref_mode == NMPC_REF_SETPOINT) {  // constant horizon: built once
+    rc = nmpc_reference_setpoint_device(h, run->sp_pos, run->sp_yaw, h->s_yref, h->s_yref_e, stream);
+    if (rc != NMPC_OK) return rc;
+  }
+  for (int k = 0; k < run->steps; k++) {
+    if (run->ref_mode == NMPC_REF_FIGURE8) {
+      rc = nmpc_reference_figure8_device(h, run->f8_t0, run->f8_amplitude, run->f8_period,
+                                         run->f8_centre, run->t_start + k * run->plant.dt,
+                                         h->s_yref, h->s_yref_e, stream);
+      if (rc != NMPC_OK) return rc;
+    }
+    rc = nmpc_solve_device(h, h->s_x0, h->s_yref, h->s_yref_e, h->s_u0, h->s_status, h->s_thrust,
+                           h->s_speed, stream);
+    if (rc != NMPC_OK) return rc;
+    // tracking error is measured against the reference position at the time of the new state:
+    // the set-point itself, or stage 1 of the horizon just used (= p_ref(t + dt))
+    const double* pref = (run->ref_mode == NMPC_REF_SETPOINT) ? run->sp_pos : h->s_yref + NZ;
+    const size_t stride = (run->ref_mode == NMPC_REF_SETPOINT) ? 3 : (size_t)N * NZ;
+    rc = launch_plant(h, &run->plant, run->x, h->s_x0, h->s_thrust, run->rotor_speed, pref, stride,
+                      h->s_status, h->qp_iters, run->stats, st);
+    if (rc != NMPC_OK) return rc;
+  }
+  return NMPC_OK;
+}
+
+int nmpc_last_outputs(nmpc_handle_t* h, const double** u0, const int32_t** status,
+                      const double** thrust, const double** speed) {
+  if (!h) return NMPC_E_INVALID;
+  if (u0) *u0 = h->s_u0;
+  if (status) *status = h->s_status;
+  if (thrust) *thrust = h->s_thrust;
+  if (speed) *speed = h->s_speed;
+  return NMPC_OK;
 }
 
 int nmpc_fp64_peak(int32_t device, double* tflops) {
