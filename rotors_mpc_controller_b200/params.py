@@ -223,3 +223,63 @@ def apply_dynamic_configuration(params: Dict[str, Any], config: Any
                           'yaw': ref['default_yaw'], 'frame': ref['frame']}
     node_meta = {'rate': params['node']['rate'], 'log_interval': params['node']['log_interval']}
     return topics, reference_defaults, node_meta
+
+
+# ------------------------------------------------------------------ slider ranges (cfg/rotors_mpc.cfg:8-92)
+def _ranges() -> Dict[str, Tuple[float, float]]:
+    r: Dict[str, Tuple[float, float]] = {
+        'solver_horizon_steps': (1, 600), 'solver_dt': (0.01, 0.2),
+        'solver_regularization': (1e-6, 0.1), 'solver_iter_max': (1, 600),
+        'vehicle_mass': (0.2, 5.0), 'vehicle_arm_length': (0.05, 1.0),
+        'vehicle_rotor_force_constant': (1e-7, 1e-4),
+        'vehicle_rotor_moment_constant': (1e-3, 0.1),
+        'vehicle_motor_min_speed': (0.0, 500.0), 'vehicle_motor_max_speed': (100.0, 2000.0),
+        'controller_thrust_min': (0.0, 20.0), 'controller_thrust_max': (0.0, 40.0),
+        'world_gravity': (5.0, 15.0), 'reference_position_z': (0.0, 10.0),
+        'reference_yaw': (-3.1416, 3.1416), 'node_rate': (10.0, 200.0),
+        'node_log_interval': (0.1, 10.0),
+    }
+    for a in 'xyz':
+        r[f'solver_position_weight_{a}'] = (0.0, 50.0)
+        r[f'solver_velocity_weight_{a}'] = (0.0, 10.0)
+        r[f'solver_rate_weight_{a}'] = (0.0, 20.0)
+        r[f'solver_terminal_weight_p{a}'] = (0.0, 50.0)
+        r[f'solver_terminal_weight_v{a}'] = (0.0, 20.0)
+        r[f'solver_terminal_weight_w{a}'] = (0.0, 20.0)
+        r[f'vehicle_drag_{a}'] = (-0.5, 0.5)
+        r[f'reference_velocity_{a}'] = (-5.0, 5.0)
+        r[f'reference_acceleration_{a}'] = (-10.0, 10.0)
+    for a in 'xy':
+        r[f'reference_position_{a}'] = (-10.0, 10.0)
+    for a in 'wxyz':
+        r[f'solver_quat_weight_{a}'] = (0.0, 20.0)
+        r[f'solver_terminal_weight_q{a}'] = (0.0, 50.0)
+    for i in '1234':
+        r[f'solver_control_weight_f{i}'] = (0.0, 5.0)
+    for a in ('xx', 'yy', 'zz'):
+        r[f'vehicle_inertia_{a}'] = (0.0, 0.1)
+    for a in ('xy', 'xz', 'yx', 'yz', 'zx', 'zy'):
+        r[f'vehicle_inertia_{a}'] = (-0.05, 0.05)
+    return r
+
+
+DYNAMIC_RANGES = _ranges()
+
+
+def clamp_dynamic_configuration(config: Any) -> List[str]:
+    """Clamp the numeric fields of a dynamic_reconfigure-style ``config`` object to the slider
+    ranges of ``cfg/rotors_mpc.cfg:8-92`` in place -- what the dynamic_reconfigure server does
+    before ``_reconfigure_cb`` (``nodes/mpc_controller_node:166-198``) sees the values.  Returns
+    the names that were changed.  The reference then rebuilds and recompiles the acados solver
+    on every event (:196-198); here ``BatchedPositionNMPC.reconfigure`` swaps constants in the
+    existing handle (``nmpc_reconfigure``) unless the horizon length changed."""
+    changed = []
+    for name, (lo, hi) in DYNAMIC_RANGES.items():
+        if not hasattr(config, name):
+            continue
+        v = getattr(config, name)
+        c = min(max(v, type(v)(lo)), type(v)(hi))
+        if c != v:
+            setattr(config, name, c)
+            changed.append(name)
+    return changed

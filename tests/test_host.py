@@ -227,3 +227,23 @@ def test_no_cpu_fallback(built, params):
     assert ei.value.code == _abi.E_NODEVICE
     src = ''.join(p.read_text() for p in (ROOT / 'rotors_mpc_controller_b200').glob('*.py'))
     assert 'oracle' not in src.replace('the oracle', '')   # product never imports oracle/
+
+
+def test_slider_ranges_cover_every_numeric_cfg_field(params):
+    """DYNAMIC_RANGES mirrors cfg/rotors_mpc.cfg:8-92 (67 numeric sliders) and clamping acts
+    like the dynamic_reconfigure server: out-of-range values are pulled to the edge."""
+    import copy
+    from types import SimpleNamespace
+    from rotors_mpc_controller_b200 import (DYNAMIC_RANGES, apply_dynamic_configuration,
+                                            clamp_dynamic_configuration)
+    assert len(DYNAMIC_RANGES) == 67
+    assert DYNAMIC_RANGES['solver_horizon_steps'] == (1, 600)
+    assert DYNAMIC_RANGES['solver_terminal_weight_qz'] == (0.0, 50.0)
+    assert DYNAMIC_RANGES['vehicle_motor_max_speed'] == (100.0, 2000.0)
+    cfg = SimpleNamespace(solver_horizon_steps=900, solver_dt=0.001, vehicle_mass=0.68,
+                          solver_position_weight_x=75.0, node_rate=60.0, topic_state='/odom')
+    changed = clamp_dynamic_configuration(cfg)
+    assert sorted(changed) == ['solver_dt', 'solver_horizon_steps', 'solver_position_weight_x']
+    assert cfg.solver_horizon_steps == 600 and isinstance(cfg.solver_horizon_steps, int)
+    assert cfg.solver_dt == 0.01 and cfg.solver_position_weight_x == 50.0
+    assert cfg.vehicle_mass == 0.68 and cfg.topic_state == '/odom'
