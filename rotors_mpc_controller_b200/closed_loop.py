@@ -194,7 +194,7 @@ class ClosedLoop:
             out.append(torch.as_tensor(_DeviceArray(p.value, shape, ts), device=self.dev).clone())
         return tuple(out)
 
-    def summary(self, group=None) -> Dict[str, float]:
+    def summary(self, group=None, reduce: bool = True) -> Dict[str, float]:
         """Reduce the per-problem statistics on the device (and over ranks when a process group
         is initialised): the <=64-entry vector north_star lets NCCL carry."""
         torch = self._torch
@@ -205,7 +205,8 @@ class ClosedLoop:
             s[:, 6].sum(), s[:, 7].sum(), (s[:, 2] > 0).sum().to(torch.float64)])
         mx = torch.stack([s[:, 5].max(), s[:, 1].max()])
         import torch.distributed as dist
-        if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        if (reduce and dist.is_available() and dist.is_initialized()
+                and dist.get_world_size(group) > 1):
             dist.all_reduce(vec, op=dist.ReduceOp.SUM, group=group)
             dist.all_reduce(mx, op=dist.ReduceOp.MAX, group=group)
         v, m = vec.cpu().numpy(), mx.cpu().numpy()
