@@ -86,14 +86,14 @@ constexpr int SP_LD = 14;  // padded leading dimension of P and K rows (16-byte 
 constexpr int SM_LD = 18;  // padded leading dimension of the staged M rows
 struct SmemLayout {
   static constexpr int P = 0;                    // 13 x 14
-  static constexpr int M = P + NX * SP_LD;       // 13 x 18
-  static constexpr int K = M + NX * SM_LD;       // 4 x 14
+  static constexpr int M = P + NX * SP_LD;       // 2 x (13 x 14 + 2) double-buffered + 3 x 4
+  static constexpr int K = M + 384;              // 4 x 14   (M: two 13 x 14 tiles + W_p, see factor_sweep)
   static constexpr int p = K + NU * SP_LD;       // 13 (+1)
   static constexpr int wv = p + 14;              // 13 (+1)
   static constexpr int xA = wv + 14;             // 13 (+1) forward-sweep state, ping
   static constexpr int xB = xA + 14;             // pong
   static constexpr int u = xB + 14;              // 4
-  static constexpr int total = u + 4;            // 548 elements
+  static constexpr int total = u + 4;            // 698 elements
 };
 
 template <typename T>
