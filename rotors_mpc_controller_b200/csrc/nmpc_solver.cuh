@@ -85,15 +85,16 @@ __host__ __device__ inline WsLayout make_layout(int N) {
 constexpr int SP_LD = 14;  // padded leading dimension of P and K rows (16-byte aligned rows)
 constexpr int SM_LD = 18;  // padded leading dimension of the staged M rows
 struct SmemLayout {
-  static constexpr int P = 0;                    // 13 x 14
-  static constexpr int M = P + NX * SP_LD;       // 2 x (13 x 14 + 2) double-buffered + 3 x 4
-  static constexpr int K = M + 384;              // 4 x 14   (M: two 13 x 14 tiles + W_p, see factor_sweep)
+  static constexpr int P = 0;                    // 13 x 14 cost-to-go
+  static constexpr int M = P + NX * SP_LD;       // stage buffers of the sweeps (cp.async targets):
+                                                 //   factor: 2 x (13 x 14 + 2) + 3 x 4, forward: 2 x 274
+  static constexpr int K = M + 548;              // 4 x 14
   static constexpr int p = K + NU * SP_LD;       // 13 (+1)
   static constexpr int wv = p + 14;              // 13 (+1)
   static constexpr int xA = wv + 14;             // 13 (+1) forward-sweep state, ping
   static constexpr int xB = xA + 14;             // pong
   static constexpr int u = xB + 14;              // 4
-  static constexpr int total = u + 4;            // 698 elements
+  static constexpr int total = u + 4;            // 846 elements
 };
 
 template <typename T>
@@ -288,7 +289,7 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
     *iters = it;
     return ST_QPFAIL;
   }
-  forward_sweep<T>(c, ws, L, sm, lane, true, false, L.kff, L.dx, L.du);
+  forward_sweep<T>(c, ws, L, sm, lane, true, false, true, false, L.kff, L.dx, L.du);
   // box check + interior-point start
   bool feas = true;
   T res0 = T(0);
@@ -348,7 +349,7 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
       status = (sizeof(T) == 4 && mu <= T(1e-6)) ? ST_SUCCESS : ST_QPFAIL;
       break;
     }
-    forward_sweep<T>(c, ws, L, sm, lane, false, false, L.kff, L.xa, L.ua);
+    forward_sweep<T>(c, ws, L, sm, lane, false, false, false, false, L.kff, L.xa, L.ua);
     // affine step length (division-free ratio test: the running minimum is kept as a fraction
     // an/ad and candidates are compared by cross-multiplication) and centering parameter
     T an = T(1), ad = T(1);
@@ -388,7 +389,7 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
     __syncwarp();
     // corrector increment (vector-only re-solve), accumulated onto the predictor direction
     delta_backward(c, ws, L, sm, lane);
-    forward_sweep<T>(c, ws, L, sm, lane, false, true, L.kffd, L.xa, L.ua);
+    forward_sweep<T>(c, ws, L, sm, lane, false, true, false, false, L.kffd, L.xa, L.ua);
     T bn = T(2), bd = T(1);  // ratios >= 2 cannot bind: alpha = min(1, tau * ratio), tau >= 0.995
     _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
       const T tl = ws[L.tl + i], tu = ws[L.tu + i], ll = ws[L.ll + i], lu = ws[L.lu + i];
@@ -432,10 +433,13 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
       ws[L.ll + i] += alpha * ws[L.dll + i];
       ws[L.lu + i] += alpha * ws[L.dlu + i];
     }
-    _Pragma("unroll 3") for (int i = lane; i < nxv; i += 32) ws[L.dx + i] += alpha * ws[L.xa + i];
     rho *= (T(1) - alpha);
     __syncwarp();
   }
+  // The state direction is only needed once: roll the linearised dynamics out for the final
+  // input direction, dx_{k+1} = A_k dx_k + B_k du_k + b_k (instead of updating dx every iteration).
+  __syncwarp();
+  forward_sweep<T>(c, ws, L, sm, lane, true, false, true, true, L.kff, L.dx, L.du);
   *iters = it;
   return status;
 }
