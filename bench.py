@@ -297,6 +297,12 @@ def run_gpu(args):
     import ctypes as C
     tf = C.c_double(0.0)
     _abi.check(_abi.lib().nmpc_fp64_peak(local, C.byref(tf)), 'nmpc_fp64_peak')
+    traffic = None
+    try:   # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of this workload's kernel,
+           # from the committed `ncu --set full` capture (profiles/, see its "source" field)
+        traffic = json.load(open(ROOT / 'profiles' / 'traffic.json'))['dram_bytes_per_launch']
+    except Exception:
+        pass
     achieved_gbs = bytes_per_launch / launch_s * 1e-9
     achieved_tf = flops_per_launch / launch_s * 1e-12
     line = {
@@ -311,7 +317,7 @@ def run_gpu(args):
                 'd2h_bytes_per_step': BATCH * (3 * 4 * 8 + 4)},
         'gpu_launches': launches,
         'roofline': {'bound': 'hbm', 'achieved': achieved_gbs, 'peak': hbm_peak, 'unit': 'GB/s',
-                     'frac': achieved_gbs / hbm_peak, 'traffic': None,
+                     'frac': achieved_gbs / hbm_peak, 'traffic': traffic,
                      'peak_source': 'MEASURED_PEAKS.json' if peaks else 'fallback',
                      'note': 'compulsory I/O only (8.7 KB/solve); the kernel is FP64-pipe / '
                              'shared-memory / latency bound, see roofline_fp64'},
@@ -331,7 +337,7 @@ def run_gpu(args):
             'value': v, 'unit': 'solves/s', 'cores': cores, 'kind': 'port',
             'sample': f'{n} problems of the same workload (seed 0), oracle/ C port, one process '
                       f'per core, {w:.1f} s wall'}
-    if args.extras and world == 1:
+    if world == 1 and not args.no_extras:
         line['extras'] = extras(params, dev)
     print(json.dumps(line), flush=True)
     if world > 1:
@@ -340,11 +346,13 @@ def run_gpu(args):
 
 
 def extras(params, dev):
-    """RTI throughput at large batch (not the headline workload; reported for context)."""
+    """Context numbers outside the headline workload (N=1 only): single RTI solves at large
+    batch (north_star's 10^6 solves/s target is an RTI figure) and the closed-loop Monte Carlo
+    of configs[2] at reduced length, all through the same kernel."""
     import copy
     import torch
-    from rotors_mpc_controller_b200 import BatchedPositionNMPC
-    from tests.problems import aggressive
+    from rotors_mpc_controller_b200 import BatchedPositionNMPC, ClosedLoop, Plant
+    from tests.problems import aggressive, random_states
     out = {}
     p = copy.deepcopy(params)
     p['solver']['max_sqp_iter'] = 1
@@ -368,9 +376,32 @@ def extras(params, dev):
             torch.cuda.synchronize(dev)
             ms.append(e0.elapsed_time(e1))
         it = ctl.stats()['qp_iters']
-        out[name] = {'batch': B, 'solves_per_s': B / (np.median(ms[1:]) * 1e-3),
-                     'ms': float(np.median(ms[1:])), 'mean_factorisations': float(it.mean()),
-                     'max_factorisations': int(it.max())}
+        med = float(np.median(ms[1:]))
+        out[name] = {'batch': B, 'solves_per_s': B / (med * 1e-3), 'ms': med,
+                     'mean_factorisations': float(it.mean()),
+                     'max_factorisations': int(it.max()),
+                     'fp64_tflops_algorithmic': B * (F_LIN + float(it.mean()) * F_IPM) / (med * 1e-3) * 1e-12}
+    # closed loop: 65536 vehicles x 50 control steps, warm-started RTI, RK4 plant on the device
+    cl = ClosedLoop(ctl, Plant(dt=ctl.dt, substeps=5))
+    rng = np.random.default_rng(1)
+    x = random_states(rng, B)
+    sp = x[:, 0:3] + np.concatenate([rng.uniform(-2, 2, (B, 2)), rng.uniform(-0.5, 0.5, (B, 1))], 1)
+    steps = 50
+    cl.reset(x)
+    cl.run_setpoint(5, sp)                      # warm-up
+    cl.reset(x)
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    cl.run_setpoint(steps, sp)
+    e1.record()
+    torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1)
+    s = cl.summary(reduce=False)
+    out['closed_loop_rti'] = {'vehicles': B, 'steps': steps, 'solves_per_s': B * steps / (ms * 1e-3),
+                              'ms_per_control_step': ms / steps,
+                              'mean_factorisations': s['qp_iters'] / (B * steps),
+                              'failed_solves': s['failed_solves']}
     ctl.close()
     return out
 
@@ -382,7 +413,8 @@ def main():
     ap.add_argument('--warmup', type=int, default=5)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
-    ap.add_argument('--extras', action='store_true', help='add large-batch RTI numbers')
+    ap.add_argument('--no-extras', action='store_true',
+                    help='skip the large-batch RTI / closed-loop context numbers')
     args = ap.parse_args()
     if args.impl == 'reference':
         return run_reference(args)

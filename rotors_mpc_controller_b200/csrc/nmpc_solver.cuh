@@ -317,21 +317,45 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
   int status = ST_MAXITER;
   const T inv2nb = T(1) / T(2 * nb);
 
-  for (; it < c.qp_iter_max; it++) {
-    // complementarity measure + predictor Hessian / gradient.  The slack reciprocals are
-    // computed once per iteration and reused by the affine and corrector passes.
-    T mu = T(0);
-    _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
-      const T tl = ws[L.tl + i], tu = ws[L.tu + i], ll = ws[L.ll + i], lu = ws[L.lu + i];
-      mu += tl * ll + tu * lu;
-      const T itl = rcp_(tl), itu = rcp_(tu);
-      ws[L.itl + i] = itl;
-      ws[L.itu + i] = itu;
-      const T dl = ll * itl, dw = lu * itu;
-      ws[L.Rt + i] = c.Rd[i & 3] + dl + dw;
-      ws[L.rt + i] = rho * ws[L.ru0 + i] + dl * (rho * ws[L.rbl0 + i]) + ll -
-                     dw * (rho * ws[L.rbu0 + i]) - lu;
+  // Element-wise passes over the nb = 4N box rows.  NSL rows per lane and trip: all loads of a
+  // trip are issued before any arithmetic or store.  NSL = 1 keeps the code small (the instruction
+  // cache, not the L2 latency of these short loops, is what the passes compete for).
+  constexpr int NSL = 1;
+#define NMPC_ROWS(...)                                                \
+  _Pragma("unroll 1") for (int base_ = 0; base_ < nb; base_ += 32 * NSL) { \
+    int ix[NSL];                                                      \
+    bool in[NSL];                                                     \
+    _Pragma("unroll") for (int e = 0; e < NSL; e++) {                 \
+      const int i_ = base_ + 32 * e + lane;                           \
+      in[e] = i_ < nb;                                                \
+      ix[e] = in[e] ? i_ : 0;                                         \
+    }                                                                 \
+    __VA_ARGS__                                                       \
+  }
+#define NMPC_LD(dst, off) \
+  T dst[NSL];             \
+  _Pragma("unroll") for (int e = 0; e < NSL; e++) dst[e] = ws[(off) + ix[e]];
+
+  // predictor set-up from the current (tl,tu,ll,lu): complementarity, slack reciprocals (reused
+  // by the affine and corrector passes), barrier Hessian Rt and gradient rt
+  T mu = T(0);
+  NMPC_ROWS({
+    NMPC_LD(tl, L.tl) NMPC_LD(tu, L.tu) NMPC_LD(ll, L.ll) NMPC_LD(lu, L.lu)
+    NMPC_LD(ru0, L.ru0) NMPC_LD(rbl0, L.rbl0) NMPC_LD(rbu0, L.rbu0)
+    _Pragma("unroll") for (int e = 0; e < NSL; e++) {
+      const T itl = rcp_(tl[e]), itu = rcp_(tu[e]);
+      const T dl = ll[e] * itl, dw = lu[e] * itu;
+      if (in[e]) {
+        mu += tl[e] * ll[e] + tu[e] * lu[e];
+        ws[L.itl + ix[e]] = itl;
+        ws[L.itu + ix[e]] = itu;
+        ws[L.Rt + ix[e]] = c.Rd[ix[e] & 3] + dl + dw;
+        ws[L.rt + ix[e]] = rho * ru0[e] + dl * (rho * rbl0[e]) + ll[e] - dw * (rho * rbu0[e]) - lu[e];
+      }
     }
+  })
+
+  for (; it < c.qp_iter_max; it++) {
     mu = warp_sum(mu) * inv2nb;
     if (!(mu == mu)) {
       status = ST_QPFAIL;
@@ -351,70 +375,87 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
     }
     forward_sweep<T>(c, ws, L, sm, lane, false, false, false, false, L.kff, L.xa, L.ua);
     // affine step length (division-free ratio test: the running minimum is kept as a fraction
-    // an/ad and candidates are compared by cross-multiplication) and centering parameter
+    // an/ad and candidates are compared by cross-multiplication)
     T an = T(1), ad = T(1);
-    _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
-      const T tl = ws[L.tl + i], tu = ws[L.tu + i], ll = ws[L.ll + i], lu = ws[L.lu + i];
-      const T ua = ws[L.ua + i];
-      const T dtl = ua + rho * ws[L.rbl0 + i];
-      const T dtu = -ua + rho * ws[L.rbu0 + i];
-      const T dll = -(ll * ws[L.itl + i]) * dtl - ll;
-      const T dlu = -(lu * ws[L.itu + i]) * dtu - lu;
-      ws[L.dtl + i] = dtl;
-      ws[L.dtu + i] = dtu;
-      ws[L.dll + i] = dll;
-      ws[L.dlu + i] = dlu;
-      ratio_min(an, ad, tl, dtl);
-      ratio_min(an, ad, tu, dtu);
-      ratio_min(an, ad, ll, dll);
-      ratio_min(an, ad, lu, dlu);
-    }
+    NMPC_ROWS({
+      NMPC_LD(tl, L.tl) NMPC_LD(tu, L.tu) NMPC_LD(ll, L.ll) NMPC_LD(lu, L.lu)
+      NMPC_LD(ua, L.ua) NMPC_LD(rbl0, L.rbl0) NMPC_LD(rbu0, L.rbu0)
+      NMPC_LD(itl, L.itl) NMPC_LD(itu, L.itu)
+      _Pragma("unroll") for (int e = 0; e < NSL; e++) {
+        const T dtl = ua[e] + rho * rbl0[e];
+        const T dtu = -ua[e] + rho * rbu0[e];
+        const T dll = -(ll[e] * itl[e]) * dtl - ll[e];
+        const T dlu = -(lu[e] * itu[e]) * dtu - lu[e];
+        if (in[e]) {
+          ws[L.dtl + ix[e]] = dtl;
+          ws[L.dtu + ix[e]] = dtu;
+          ws[L.dll + ix[e]] = dll;
+          ws[L.dlu + ix[e]] = dlu;
+          ratio_min(an, ad, tl[e], dtl);
+          ratio_min(an, ad, tu[e], dtu);
+          ratio_min(an, ad, ll[e], dll);
+          ratio_min(an, ad, lu[e], dlu);
+        }
+      }
+    })
     const T a_aff = warp_min(an / ad);
+    // centering parameter from the complementarity the affine step would reach
     T mu_aff = T(0);
-    _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
-      mu_aff += (ws[L.tl + i] + a_aff * ws[L.dtl + i]) * (ws[L.ll + i] + a_aff * ws[L.dll + i]) +
-                (ws[L.tu + i] + a_aff * ws[L.dtu + i]) * (ws[L.lu + i] + a_aff * ws[L.dlu + i]);
-    }
+    NMPC_ROWS({
+      NMPC_LD(tl, L.tl) NMPC_LD(tu, L.tu) NMPC_LD(ll, L.ll) NMPC_LD(lu, L.lu)
+      NMPC_LD(dtl, L.dtl) NMPC_LD(dtu, L.dtu) NMPC_LD(dll, L.dll) NMPC_LD(dlu, L.dlu)
+      _Pragma("unroll") for (int e = 0; e < NSL; e++)
+        if (in[e])
+          mu_aff += (tl[e] + a_aff * dtl[e]) * (ll[e] + a_aff * dll[e]) +
+                    (tu[e] + a_aff * dtu[e]) * (lu[e] + a_aff * dlu[e]);
+    })
     mu_aff = warp_sum(mu_aff) * inv2nb;
     T sigma = mu_aff / mu;
     sigma = sigma * sigma * sigma;
     const T smu = sigma * mu;
     // weight of the second-order term: min(1, 2 alpha_aff) (breaks Mehrotra 2-cycles)
     const T cw = fmin(T(1), T(2) * a_aff);
-    _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
-      const T sl = smu - cw * ws[L.dtl + i] * ws[L.dll + i];
-      const T su = smu - cw * ws[L.dtu + i] * ws[L.dlu + i];
-      ws[L.dr + i] = -sl * ws[L.itl + i] + su * ws[L.itu + i];
-    }
+    NMPC_ROWS({
+      NMPC_LD(dtl, L.dtl) NMPC_LD(dtu, L.dtu) NMPC_LD(dll, L.dll) NMPC_LD(dlu, L.dlu)
+      NMPC_LD(itl, L.itl) NMPC_LD(itu, L.itu)
+      _Pragma("unroll") for (int e = 0; e < NSL; e++) {
+        const T sl = smu - cw * dtl[e] * dll[e];
+        const T su = smu - cw * dtu[e] * dlu[e];
+        if (in[e]) ws[L.dr + ix[e]] = -sl * itl[e] + su * itu[e];
+      }
+    })
     __syncwarp();
     // corrector increment (vector-only re-solve), accumulated onto the predictor direction
     delta_backward(c, ws, L, sm, lane);
     forward_sweep<T>(c, ws, L, sm, lane, false, true, false, false, L.kffd, L.xa, L.ua);
     T bn = T(2), bd = T(1);  // ratios >= 2 cannot bind: alpha = min(1, tau * ratio), tau >= 0.995
-    _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
-      const T tl = ws[L.tl + i], tu = ws[L.tu + i], ll = ws[L.ll + i], lu = ws[L.lu + i];
-      const T itl = ws[L.itl + i], itu = ws[L.itu + i];
-      const T un = ws[L.ua + i];
-      const T sl = smu - cw * ws[L.dtl + i] * ws[L.dll + i];
-      const T su = smu - cw * ws[L.dtu + i] * ws[L.dlu + i];
-      const T dtl = un + rho * ws[L.rbl0 + i];
-      const T dtu = -un + rho * ws[L.rbu0 + i];
-      const T dll = -(ll * itl) * dtl + sl * itl - ll;
-      const T dlu = -(lu * itu) * dtu + su * itu - lu;
-      ws[L.dtl + i] = dtl;
-      ws[L.dtu + i] = dtu;
-      ws[L.dll + i] = dll;
-      ws[L.dlu + i] = dlu;
-      ratio_min(bn, bd, tl, dtl);
-      ratio_min(bn, bd, tu, dtu);
-      ratio_min(bn, bd, ll, dll);
-      ratio_min(bn, bd, lu, dlu);
-    }
+    bool fin = true;         // NaN anywhere must surface: comparisons drop NaNs, so test explicitly
+    NMPC_ROWS({
+      NMPC_LD(tl, L.tl) NMPC_LD(tu, L.tu) NMPC_LD(ll, L.ll) NMPC_LD(lu, L.lu)
+      NMPC_LD(itl, L.itl) NMPC_LD(itu, L.itu) NMPC_LD(un, L.ua)
+      NMPC_LD(adtl, L.dtl) NMPC_LD(adtu, L.dtu) NMPC_LD(adll, L.dll) NMPC_LD(adlu, L.dlu)
+      NMPC_LD(rbl0, L.rbl0) NMPC_LD(rbu0, L.rbu0)
+      _Pragma("unroll") for (int e = 0; e < NSL; e++) {
+        const T sl = smu - cw * adtl[e] * adll[e];
+        const T su = smu - cw * adtu[e] * adlu[e];
+        const T dtl = un[e] + rho * rbl0[e];
+        const T dtu = -un[e] + rho * rbu0[e];
+        const T dll = -(ll[e] * itl[e]) * dtl + sl * itl[e] - ll[e];
+        const T dlu = -(lu[e] * itu[e]) * dtu + su * itu[e] - lu[e];
+        if (in[e]) {
+          ws[L.dtl + ix[e]] = dtl;
+          ws[L.dtu + ix[e]] = dtu;
+          ws[L.dll + ix[e]] = dll;
+          ws[L.dlu + ix[e]] = dlu;
+          ratio_min(bn, bd, tl[e], dtl);
+          ratio_min(bn, bd, tu[e], dtu);
+          ratio_min(bn, bd, ll[e], dll);
+          ratio_min(bn, bd, lu[e], dlu);
+          fin = fin && finite_(dtl) && finite_(dll) && finite_(dlu);
+        }
+      }
+    })
     T alpha = bn / bd;
-    // NaN anywhere must surface: fmin drops NaNs, so test the directions explicitly
-    bool fin = true;
-    _Pragma("unroll 1") for (int i = lane; i < nb; i += 32)
-      fin = fin && finite_(ws[L.dtl + i]) && finite_(ws[L.dll + i]) && finite_(ws[L.dlu + i]);
     if (!__all_sync(FULL, fin)) {
       status = ST_QPFAIL;
       break;
@@ -426,16 +467,39 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
       status = ST_MINSTEP;
       break;
     }
-    _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
-      ws[L.du + i] += alpha * ws[L.ua + i];
-      ws[L.tl + i] += alpha * ws[L.dtl + i];
-      ws[L.tu + i] += alpha * ws[L.dtu + i];
-      ws[L.ll + i] += alpha * ws[L.dll + i];
-      ws[L.lu + i] += alpha * ws[L.dlu + i];
-    }
-    rho *= (T(1) - alpha);
+    // step + the predictor set-up of the next iteration (same rows, values still in registers)
+    const T rho_n = rho * (T(1) - alpha);
+    mu = T(0);
+    NMPC_ROWS({
+      NMPC_LD(du, L.du) NMPC_LD(ua, L.ua)
+      NMPC_LD(tl, L.tl) NMPC_LD(tu, L.tu) NMPC_LD(ll, L.ll) NMPC_LD(lu, L.lu)
+      NMPC_LD(dtl, L.dtl) NMPC_LD(dtu, L.dtu) NMPC_LD(dll, L.dll) NMPC_LD(dlu, L.dlu)
+      NMPC_LD(ru0, L.ru0) NMPC_LD(rbl0, L.rbl0) NMPC_LD(rbu0, L.rbu0)
+      _Pragma("unroll") for (int e = 0; e < NSL; e++) {
+        const T ntl = tl[e] + alpha * dtl[e], ntu = tu[e] + alpha * dtu[e];
+        const T nll = ll[e] + alpha * dll[e], nlu = lu[e] + alpha * dlu[e];
+        const T itl = rcp_(ntl), itu = rcp_(ntu);
+        const T dl = nll * itl, dw = nlu * itu;
+        if (in[e]) {
+          ws[L.du + ix[e]] = du[e] + alpha * ua[e];
+          ws[L.tl + ix[e]] = ntl;
+          ws[L.tu + ix[e]] = ntu;
+          ws[L.ll + ix[e]] = nll;
+          ws[L.lu + ix[e]] = nlu;
+          mu += ntl * nll + ntu * nlu;
+          ws[L.itl + ix[e]] = itl;
+          ws[L.itu + ix[e]] = itu;
+          ws[L.Rt + ix[e]] = c.Rd[ix[e] & 3] + dl + dw;
+          ws[L.rt + ix[e]] =
+              rho_n * ru0[e] + dl * (rho_n * rbl0[e]) + nll - dw * (rho_n * rbu0[e]) - nlu;
+        }
+      }
+    })
+    rho = rho_n;
     __syncwarp();
   }
+#undef NMPC_ROWS
+#undef NMPC_LD
   // The state direction is only needed once: roll the linearised dynamics out for the final
   // input direction, dx_{k+1} = A_k dx_k + B_k du_k + b_k (instead of updating dx every iteration).
   __syncwarp();
