@@ -87,14 +87,14 @@ constexpr int SM_LD = 18;  // padded leading dimension of the staged M rows
 struct SmemLayout {
   static constexpr int P = 0;                    // 13 x 14 cost-to-go
   static constexpr int M = P + NX * SP_LD;       // stage buffers of the sweeps (cp.async targets):
-                                                 //   factor: 2 x (13 x 14 + 2) + 3 x 4, forward: 2 x 274
-  static constexpr int K = M + 548;              // 4 x 14
+                                                 //   factor: 2 x 208 + 224, forward: 2 x 274
+  static constexpr int K = M + 640;              // 4 x 14
   static constexpr int p = K + NU * SP_LD;       // 13 (+1)
   static constexpr int wv = p + 14;              // 13 (+1)
   static constexpr int xA = wv + 14;             // 13 (+1) forward-sweep state, ping
   static constexpr int xB = xA + 14;             // pong
   static constexpr int u = xB + 14;              // 4
-  static constexpr int total = u + 4;            // 846 elements
+  static constexpr int total = u + 4;            // 938 elements
 };
 
 template <typename T>
