@@ -35,6 +35,11 @@ struct WsLayout {
   int total;
 };
 
+// One record per stage keeps what the sweeps stream together contiguous (one 16-byte-chunked
+// cp.async range per stage): M_k at L.M + k*REC, K_k at L.K + k*REC.
+constexpr int REC_K = NX * NZ + 1;       // 222: offset of K_k inside a record (even)
+constexpr int REC = REC_K + NU * NX;     // 274
+
 __host__ __device__ inline WsLayout make_layout(int N) {
   WsLayout L;
   L.N = N;
@@ -45,8 +50,8 @@ __host__ __device__ inline WsLayout make_layout(int N) {
     return r;
   };
   const int nx = (N + 1) * NX, nu = N * NU;
-  L.M = take(N * NX * NZ);
-  L.K = take(N * NU * NX);
+  L.M = take(N * REC);  // stage records [M_k (13x17) | pad | K_k (4x13)], REC elements each
+  L.K = L.M + REC_K;
   L.Qi = take(N * 16);
   L.kff = take(nu);
   L.kffd = take(nu);
@@ -212,7 +217,7 @@ __device__ __forceinline__ void linearize(const DevCfg<T>& c, T* __restrict__ ws
     erk_column<T, NS>(c, x, u, s, su);
     if (lane < NZ) {
 #pragma unroll
-      for (int i = 0; i < NX; i++) M[(k * NX + i) * NZ + lane] = s[i];
+      for (int i = 0; i < NX; i++) M[k * REC + i * NZ + lane] = s[i];
     }
     T xl = x[0];  // every lane holds the same nominal x; lane i writes component i
 #pragma unroll
