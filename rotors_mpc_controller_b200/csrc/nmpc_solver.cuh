@@ -37,8 +37,9 @@ struct WsLayout {
 
 // One record per stage keeps what the sweeps stream together contiguous (one 16-byte-chunked
 // cp.async range per stage): M_k at L.M + k*REC, K_k at L.K + k*REC.
-constexpr int REC_K = NX * NZ + 1;       // 222: offset of K_k inside a record (even)
-constexpr int REC = REC_K + NU * NX;     // 274
+constexpr int M_LD = NZ + 1;             // 18: row stride of M_k (rows start 16-byte aligned)
+constexpr int REC_K = NX * M_LD;         // 234: offset of K_k inside a record
+constexpr int REC = REC_K + NU * NX;     // 286
 
 __host__ __device__ inline WsLayout make_layout(int N) {
   WsLayout L;
@@ -50,7 +51,7 @@ __host__ __device__ inline WsLayout make_layout(int N) {
     return r;
   };
   const int nx = (N + 1) * NX, nu = N * NU;
-  L.M = take(N * REC);  // stage records [M_k (13x17) | pad | K_k (4x13)], REC elements each
+  L.M = take(N * REC);  // stage records [M_k (13 rows of 17+1) | K_k (4x13)], REC elements each
   L.K = L.M + REC_K;
   L.Qi = take(N * 16);
   L.kff = take(nu);
@@ -88,18 +89,17 @@ __host__ __device__ inline WsLayout make_layout(int N) {
 
 // Per-warp shared-memory tile (elements of T).
 constexpr int SP_LD = 14;  // padded leading dimension of P and K rows (16-byte aligned rows)
-constexpr int SM_LD = 18;  // padded leading dimension of the staged M rows
 struct SmemLayout {
   static constexpr int P = 0;                    // 13 x 14 cost-to-go
   static constexpr int M = P + NX * SP_LD;       // stage buffers of the sweeps (cp.async targets):
-                                                 //   factor: 2 x 208 + 224, forward: 2 x 274
-  static constexpr int K = M + 640;              // 4 x 14
+                                                 //   factor: 2 x 234 + 224, forward: 2 x 286
+  static constexpr int K = M + 692;              // 4 x 14
   static constexpr int p = K + NU * SP_LD;       // 13 (+1)
   static constexpr int wv = p + 14;              // 13 (+1)
   static constexpr int xA = wv + 14;             // 13 (+1) forward-sweep state, ping
   static constexpr int xB = xA + 14;             // pong
   static constexpr int u = xB + 14;              // 4
-  static constexpr int total = u + 4;            // 938 elements
+  static constexpr int total = u + 4;            // 990 elements
 };
 
 template <typename T>
@@ -215,9 +215,9 @@ __device__ __forceinline__ void linearize(const DevCfg<T>& c, T* __restrict__ ws
       su[i] = (lane == i) ? T(1) : T(0);
     }
     erk_column<T, NS>(c, x, u, s, su);
-    if (lane < NZ) {
+    if (lane < M_LD) {  // lane 17 zeroes the row padding
 #pragma unroll
-      for (int i = 0; i < NX; i++) M[k * REC + i * NZ + lane] = s[i];
+      for (int i = 0; i < NX; i++) M[k * REC + i * M_LD + lane] = (lane < NZ) ? s[i] : T(0);
     }
     T xl = x[0];  // every lane holds the same nominal x; lane i writes component i
 #pragma unroll
