@@ -316,15 +316,19 @@ def run_gpu(args):
                 'h2d_bytes_per_step': BATCH * (13 + HORIZON * 17 + 13) * 8,
                 'd2h_bytes_per_step': BATCH * (3 * 4 * 8 + 4)},
         'gpu_launches': launches,
-        'roofline': {'bound': 'hbm', 'achieved': achieved_gbs, 'peak': hbm_peak, 'unit': 'GB/s',
-                     'frac': achieved_gbs / hbm_peak, 'traffic': traffic,
-                     'peak_source': 'MEASURED_PEAKS.json' if peaks else 'fallback',
-                     'note': 'compulsory I/O only (8.7 KB/solve); the kernel is FP64-pipe / '
-                             'shared-memory / latency bound, see roofline_fp64'},
-        'roofline_fp64': {'bound': 'fp64', 'achieved': achieved_tf, 'peak': tf.value,
-                          'unit': 'TFLOP/s', 'frac': achieved_tf / tf.value if tf.value else None,
-                          'peak_source': 'nmpc_fp64_peak DFMA micro-benchmark, same run',
-                          'flops_per_solve': flops_per_launch / BATCH},
+        # the bound that limits this kernel is the FP64 pipe (north_star: no tensor cores, FP64
+        # FLOP/s and HBM GB/s against peak); the HBM roofline of the same launch is beside it
+        'roofline': {'bound': 'fp64', 'achieved': achieved_tf, 'peak': tf.value,
+                     'unit': 'TFLOP/s', 'frac': achieved_tf / tf.value if tf.value else None,
+                     'traffic': traffic,
+                     'peak_source': 'nmpc_fp64_peak: DFMA micro-benchmark on this GPU, same run '
+                                    '(MEASURED_PEAKS.json holds no FP64 figure)',
+                     'flops_per_solve': flops_per_launch / BATCH,
+                     'note': 'algorithmic FP64 flops (DESIGN.md section 5) / CUDA-event launch time'},
+        'roofline_hbm': {'bound': 'hbm', 'achieved': achieved_gbs, 'peak': hbm_peak, 'unit': 'GB/s',
+                         'frac': achieved_gbs / hbm_peak, 'traffic': traffic,
+                         'peak_source': 'MEASURED_PEAKS.json' if peaks else 'fallback',
+                         'note': 'compulsory I/O only (8.7 KB/solve): the path is not HBM bound'},
         'solver_stats': {'mean_sqp_iters': mean_sqp, 'mean_riccati_factorisations': mean_qp,
                          'status_ok_frac': ok_count / n_solves},
         'wall_s_timed_region': wall,
@@ -381,6 +385,30 @@ def extras(params, dev):
                      'mean_factorisations': float(it.mean()),
                      'max_factorisations': int(it.max()),
                      'fp64_tflops_algorithmic': B * (F_LIN + float(it.mean()) * F_IPM) / (med * 1e-3) * 1e-12}
+    # the headline workload at 16x the batch: the share of the batch-4096 launch that is the
+    # tail of its longest problems (no work left to hide them behind) disappears
+    ps = copy.deepcopy(params)
+    cs = BatchedPositionNMPC(ps, batch=B, device=dev.index)
+    X, Y, Z = (torch.as_tensor(a, device=dev) for a in make_inputs(0, B, cs.hover_thrust))
+    ms = []
+    for rep in range(3):
+        cs.invalidate()
+        torch.cuda.synchronize(dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        cs.solve(X, Y, Z)
+        e1.record()
+        torch.cuda.synchronize(dev)
+        ms.append(e0.elapsed_time(e1))
+    st = cs.stats()
+    med = float(np.median(ms[1:]))
+    out['sqp_cfg2_batch65536'] = {
+        'batch': B, 'solves_per_s': B / (med * 1e-3), 'ms': med,
+        'mean_factorisations': float(st['qp_iters'].mean()),
+        'max_factorisations': int(st['qp_iters'].max()),
+        'fp64_tflops_algorithmic': B * (float(st['sqp_iters'].mean()) * F_LIN
+                                        + float(st['qp_iters'].mean()) * F_IPM) / (med * 1e-3) * 1e-12}
+    cs.close()
     # closed loop: 65536 vehicles x 50 control steps, warm-started RTI, RK4 plant on the device
     cl = ClosedLoop(ctl, Plant(dt=ctl.dt, substeps=5))
     rng = np.random.default_rng(1)

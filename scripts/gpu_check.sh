@@ -1,5 +1,6 @@
 #!/bin/bash
-# One gpurun call: GPU parity tests, smoke, the bench (both arms), launch list + full ncu captures.
+# One gpurun call: GPU parity tests, smoke, the bench (both arms) and the ncu launch list of the
+# bench command.  The full captures are separate calls (scripts/gpu_ncu_bench.sh, gpu_ncu.sh).
 set -o pipefail
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/smi.txt 2>&1
@@ -11,8 +12,3 @@ BCMD="python bench.py --steps 3 --warmup 3 --no-cpu --no-extras"
 timeout 300 $BCMD > gpurun_out/plain.log 2>&1 &&
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/launches.csv $BCMD > gpurun_out/ncu_launches.log 2>&1
 echo "ncu launches rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:nmpc_solve -s 4 -c 1 -o gpurun_out/prof_bench -f $BCMD > gpurun_out/ncu_full_bench.log 2>&1
-echo "ncu full (bench kernel) rc=$?"
-timeout 300 python scripts/prof_rti.py 16384 > gpurun_out/prof_plain.log 2>&1 &&
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:nmpc_solve -s 1 -c 1 -o gpurun_out/prof_rti -f python scripts/prof_rti.py 16384 > gpurun_out/ncu_full.log 2>&1
-echo "ncu full (rti) rc=$?"; cat gpurun_out/prof_plain.log
