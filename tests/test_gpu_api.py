@@ -1,0 +1,179 @@
+"""GPU tests of the handle's API surface beyond a plain solve: ragged batch sizes, fast
+``reconfigure`` (constants swap, no code generation), run-time bounds, masked
+invalidation, warm-start store round trip and the C ABI's error codes.  Checked against the CPU
+oracle with the tolerances of tests/test_gpu_parity.py (FP64: |u0 - oracle| <= 1e-8, statuses
+identical)."""
+import copy
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from tests.problems import aggressive, random_states, setpoint_refs
+
+pytestmark = pytest.mark.gpu
+
+TOL_U = 1e-8
+
+
+@pytest.fixture(scope='module')
+def O(built):
+    from oracle import oracle
+    return oracle
+
+
+def _ctl(params, B):
+    from rotors_mpc_controller_b200 import BatchedPositionNMPC
+    return BatchedPositionNMPC(copy.deepcopy(params), batch=B)
+
+
+@pytest.mark.parametrize('B', [1, 3, 5, 127, 130, 1777])
+def test_ragged_batches(params, O, B):
+    """Batches that do not fill a CTA (4 warps), a wave (1 776 resident warps) or a warp queue."""
+    ctl = _ctl(params, B)
+    rng = np.random.default_rng(B)
+    x0, yref, yref_e = aggressive(rng, B, 20, ctl.hover_thrust)
+    u0, st = ctl.solve(x0, yref, yref_e)
+    ob = O.OracleBatch(O.config_from_params(params), B)
+    ur, sr, thr, _ = ob.solve(x0, yref, yref_e)
+    assert np.array_equal(st, sr)
+    assert np.max(np.abs(u0 - ur)) < TOL_U
+    assert np.max(np.abs(ctl.command()[0] - thr)) < TOL_U
+    assert np.array_equal(ctl.stats()['qp_iters'], ob.qp_iters)
+    ctl.close()
+
+
+def test_reconfigure_swaps_constants(params, O):
+    """controller.py:63-172 rebuilds and recompiles the solver on every slider move; here the same
+    call swaps the constant block of the handle.  Results must follow the NEW parameters and the
+    warm start must be dropped (controller.py:167)."""
+    B = 96
+    ctl = _ctl(params, B)
+    rng = np.random.default_rng(5)
+    x0 = random_states(rng, B)
+    yref, yref_e = setpoint_refs(rng, x0, 20, ctl.hover_thrust)
+    ctl.solve(x0, yref, yref_e)
+    assert ctl.trajectories()[2].all()
+    launches = ctl.kernel_launches
+
+    p2 = copy.deepcopy(params)
+    p2['solver']['position_weight'] = [25.0, 20.0, 4.0]
+    p2['solver']['control_weight'] = [0.5, 0.6, 0.7, 0.8]
+    p2['solver']['terminal_weight'] = [float(v) * 1.5 for v in np.arange(1, 14)]
+    p2['solver']['regularization'] = 2.0e-2
+    p2['solver']['iter_max'] = 80
+    p2['vehicle']['mass'] = 0.9
+    p2['vehicle']['motor_max_speed'] = 700.0
+    ctl.reconfigure(p2)
+    assert not ctl.trajectories()[2].any()              # warm start invalidated
+    assert abs(ctl.hover_thrust - 0.9 * ctl.gravity / 4.0) < 1e-12
+    yref[:, :, 13:17] = ctl.hover_thrust
+    u0, st = ctl.solve(x0, yref, yref_e)
+    assert ctl.kernel_launches == launches + 1          # same handle, no rebuild
+    ob = O.OracleBatch(O.config_from_params(p2), B)
+    ur, sr, thr, spr = ob.solve(x0, yref, yref_e)
+    assert np.array_equal(st, sr)
+    assert np.max(np.abs(u0 - ur)) < TOL_U
+    assert np.max(np.abs(ctl.command()[0] - thr)) < TOL_U
+    lo, hi = ctl.input_bounds
+    assert np.allclose(hi, ctl.rotor_force_constant * 700.0 ** 2)
+
+    # a different horizon needs new buffers: the handle is replaced behind the same object
+    p3 = copy.deepcopy(p2)
+    p3['solver']['horizon_steps'] = 12
+    ctl.reconfigure(p3)
+    assert ctl.horizon == 12
+    yr, yre = setpoint_refs(rng, x0, 12, ctl.hover_thrust)
+    u0, st = ctl.solve(x0, yr, yre)
+    ob = O.OracleBatch(O.config_from_params(p3), B)
+    ur, sr, _, _ = ob.solve(x0, yr, yre)
+    assert np.array_equal(st, sr)
+    assert np.max(np.abs(u0 - ur)) < TOL_U
+    ctl.close()
+
+
+def test_set_bounds_at_run_time(params, O):
+    B = 64
+    ctl = _ctl(params, B)
+    rng = np.random.default_rng(6)
+    x0, yref, yref_e = aggressive(rng, B, 20, ctl.hover_thrust)
+    ctl.set_bounds(0.5, 3.0)
+    u0, st = ctl.solve(x0, yref, yref_e)
+    ob = O.OracleBatch(O.config_from_params(params, thrust_box=(0.5, 3.0)), B)
+    ur, sr, thr, _ = ob.solve(x0, yref, yref_e)
+    assert np.array_equal(st, sr)
+    assert np.max(np.abs(u0 - ur)) < TOL_U
+    ok = st == 0
+    assert ok.any()
+    assert u0[ok].min() >= 0.5 - 1e-9 and u0[ok].max() <= 3.0 + 1e-9
+    assert (np.abs(u0[ok] - 0.5) < 1e-6).any() or (np.abs(u0[ok] - 3.0) < 1e-6).any()
+    from rotors_mpc_controller_b200 import _abi
+    with pytest.raises(_abi.NmpcError):
+        ctl.set_bounds(2.0, 1.0)                          # empty box
+    ctl.close()
+
+
+def test_masked_invalidate_and_store_round_trip(params, O):
+    """nmpc_invalidate(mask) is the batched form of `_prev_solution_valid = False`
+    (controller.py:449, :167); get/set_trajectories move the warm-start store between handles."""
+    B = 80
+    ctl = _ctl(params, B)
+    cfg = O.config_from_params(params)
+    ob = O.OracleBatch(cfg, B)
+    rng = np.random.default_rng(7)
+    x0 = random_states(rng, B)
+    yref, yref_e = setpoint_refs(rng, x0, 20, ctl.hover_thrust)
+    ctl.solve(x0, yref, yref_e)
+    ob.solve(x0, yref, yref_e)
+    mask = (np.arange(B) % 3 == 0).astype(np.uint8)
+    ctl.invalidate(mask)
+    ob.valid[mask.astype(bool)] = 0
+    assert np.array_equal(ctl.trajectories()[2], ob.valid.astype(bool))
+    xs, us, vs = ctl.trajectories()
+    twin = _ctl(params, B)
+    twin.set_trajectories(xs, us, vs)
+    x1 = x0 + 0.01 * rng.normal(size=x0.shape)
+    x1[:, 6:10] /= np.linalg.norm(x1[:, 6:10], axis=1, keepdims=True)
+    u0, st = ctl.solve(x1, yref, yref_e)
+    u0 = u0.copy()
+    ur, sr, _, _ = ob.solve(x1, yref, yref_e)
+    assert np.array_equal(st, sr)
+    assert np.max(np.abs(u0 - ur)) < TOL_U
+    ut, stt = twin.solve(x1, yref, yref_e)
+    assert np.array_equal(ut, u0) and np.array_equal(stt, st)   # same store -> same bits
+    ctl.close()
+    twin.close()
+
+
+def test_abi_error_codes(params, built):
+    """Every entry point answers a bad argument with NMPC_E_INVALID instead of crashing; a
+    per-problem solver failure is data (status), never an error code."""
+    from rotors_mpc_controller_b200 import _abi
+    from rotors_mpc_controller_b200.controller import abi_config, controller_params_from_dict
+    lib = _abi.lib()
+    cfg = abi_config(controller_params_from_dict(params), params['solver'])
+    h = C.c_void_p()
+    assert lib.nmpc_create(C.byref(cfg), 0, 0, C.byref(h)) == -1            # empty batch
+    assert lib.nmpc_create(C.byref(cfg), 4, 99, C.byref(h)) == -1           # no such device
+    assert lib.nmpc_create(None, 4, 0, C.byref(h)) == -1
+    bad = copy.copy(cfg)
+    bad.N = 601                                                               # slider maximum is 600
+    assert lib.nmpc_create(C.byref(bad), 4, 0, C.byref(h)) == -1
+    bad = copy.copy(cfg)
+    bad.lbu[0] = bad.ubu[0] + 1.0
+    assert lib.nmpc_create(C.byref(bad), 4, 0, C.byref(h)) == -1
+    assert lib.nmpc_create(C.byref(cfg), 4, 0, C.byref(h)) == 0
+    out = np.zeros(64)
+    st = np.zeros(4, np.int32)
+    assert lib.nmpc_solve_host(h, None, _abi.ptr(out), _abi.ptr(out), _abi.ptr(out),
+                               _abi.ptr(st), None, None) == -1
+    assert lib.nmpc_solve_host(None, _abi.ptr(out), _abi.ptr(out), _abi.ptr(out), _abi.ptr(out),
+                               _abi.ptr(st), None, None) == -1
+    other = copy.copy(cfg)
+    other.N = cfg.N + 1
+    assert lib.nmpc_reconfigure(h, C.byref(other)) == -1                     # shape change
+    assert lib.nmpc_set_bounds(h, None, None) == -1
+    assert lib.nmpc_batch(h) == 4 and lib.nmpc_horizon(h) == cfg.N
+    assert lib.nmpc_batch(None) == -1
+    assert b'invalid' in lib.nmpc_strerror(-1)
+    assert lib.nmpc_destroy(h) == 0
