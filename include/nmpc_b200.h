@@ -59,7 +59,9 @@ typedef struct nmpc_config {
   int32_t max_sqp_iter;    /* 1 = SQP_RTI (reference); >1 = SQP until step <= sqp_tol */
   int32_t nan_status;      /* status reported when NaNs appear in the iterate (4 or 1) */
   int32_t precision;       /* NMPC_PRECISION_F64 | NMPC_PRECISION_F32 */
-  int32_t reserved;
+  int32_t ipm_warm_start;  /* 1: inside one solve with max_sqp_iter > 1, QPs after the first start the
+                              interior point from the previous QP's slacks / multipliers (see
+                              NMPC_WARM_*); 0: every QP starts cold.  RTI solves are not affected */
   double dt;
   double W[17];            /* stage weights [p(3) v(3) q(4) w(3) u(4)] (controller.py:234-240) */
   double We[13];           /* terminal weights (controller.py:241) */
@@ -78,6 +80,15 @@ typedef struct nmpc_config {
   double sqp_tol;          /* inf-norm step tolerance when max_sqp_iter > 1 */
   double ipm_tol;          /* interior-point complementarity / residual tolerance */
 } nmpc_config_t;
+
+/* Interior-point warm start between the QPs of one SQP run: used when the previous QP's
+ * interior-point loop converged and the previous SQP step (inf-norm) was <= NMPC_WARM_STEP_MAX;
+ * slacks and multipliers are clipped to eps = clamp(NMPC_WARM_KAPPA * step, NMPC_WARM_EPS_MIN,
+ * NMPC_WARM_EPS_MAX).  The QP solutions are the same to the interior-point tolerance. */
+#define NMPC_WARM_KAPPA 0.1
+#define NMPC_WARM_STEP_MAX 0.3
+#define NMPC_WARM_EPS_MIN 1e-8
+#define NMPC_WARM_EPS_MAX 0.1
 
 typedef struct nmpc_handle nmpc_handle_t;
 

@@ -62,7 +62,17 @@ typedef struct {
   double sqp_tol;     /* inf-norm step tolerance for max_sqp_iter>1 */
   double ipm_tol;     /* complementarity / residual tolerance of the QP IPM */
   int nan_status;     /* status reported when NaNs appear (4 = QP failure, or 1) */
+  int ipm_warm;       /* 1: QPs after the first of an SQP run (max_sqp_iter > 1) warm-start the
+                         interior point from the previous QP's (t, lam), see ORC_WARM_* */
 } orc_config;
+
+/* Warm start between the QPs of one SQP run: used when the previous QP's interior-point loop
+ * converged and the previous SQP step was <= ORC_WARM_STEP_MAX (the active set is settling);
+ * the iterate is clipped to eps = clamp(ORC_WARM_KAPPA * step, ORC_WARM_EPS_MIN, ORC_WARM_EPS_MAX). */
+#define ORC_WARM_KAPPA 0.1
+#define ORC_WARM_STEP_MAX 0.3
+#define ORC_WARM_EPS_MIN 1e-8
+#define ORC_WARM_EPS_MAX 0.1
 
 /* continuous model, controller.py:267-355 */
 void orc_f(const orc_config *c, const double *x, const double *u, double *f);
@@ -99,6 +109,9 @@ void orc_build_qp(const orc_config *c, const double *xtraj, const double *utraj,
  * Returns 0 ok, 2 iteration cap (tolerated by RTI), 3 min step, 4 NaN. */
 int orc_qp_solve(const orc_qp *qp, int iter_max, double tol, double *dx, double *du, double *lam_l,
                  double *lam_u, int *iters);
+int orc_qp_solve_warm(const orc_qp *qp, int iter_max, double tol, double *dx, double *du,
+                      double *lam_l, double *lam_u, double *t_l_io, double *t_u_io, double warm_eps,
+                      int *ipm_converged, int *iters);
 
 /* One PositionNMPC.solve() (controller.py:385-463) for a single problem.
  * xtraj/utraj/valid are the warm-start store (in/out).  x0 must already hold the

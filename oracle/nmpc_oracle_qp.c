@@ -310,6 +310,20 @@ static double corr_weight(double a) { return fmin(1.0, 2.0 * a); }
  * corrector is a vector-only re-solve added to the predictor direction. */
 int orc_qp_solve(const orc_qp *qp, int iter_max, double tol, double *dx, double *du, double *lam_l,
                  double *lam_u, int *iters) {
+  return orc_qp_solve_warm(qp, iter_max, tol, dx, du, lam_l, lam_u, NULL, NULL, 0.0, NULL, iters);
+}
+
+/* The same solver with an optional warm start of the interior-point iterate (used between the QPs
+ * of one SQP run, see orc_solve): with warm_eps > 0 the loop starts from the previous QP's slacks
+ * (t_l_io, t_u_io) and multipliers (lam_l, lam_u), pushed away from the boundary,
+ *     t = max(t_prev, eps),  lam = max(lam_prev, eps),
+ * instead of t = max(slack, 0.1), lam = 0.1 / t.  Phase 0 is unchanged, so the primal start and
+ * the residual bookkeeping (rho) are the same.  On return t_l_io / t_u_io (when given) hold the
+ * slacks of the final iterate and *ipm_converged tells whether the interior-point loop ran and
+ * met its tolerance (only then is the iterate a valid warm start for the next QP). */
+int orc_qp_solve_warm(const orc_qp *qp, int iter_max, double tol, double *dx, double *du,
+                      double *lam_l, double *lam_u, double *t_l_io, double *t_u_io, double warm_eps,
+                      int *ipm_converged, int *iters) {
   const int N = qp->N;
   const int nb = N * NU;
   ric_ws ws;
@@ -325,6 +339,7 @@ int orc_qp_solve(const orc_qp *qp, int iter_max, double tol, double *dx, double 
   double *xa = ru0 + nb, *xc = xa + (size_t)(N + 1) * NX;
   int status = ORC_MAXITER;
   int it = 0;
+  if (ipm_converged) *ipm_converged = 0;
 
   /* Phase 0: equality-constrained QP (box ignored).  If its solution respects the box it
    * is the QP solution (strict convexity) and no interior-point iteration is needed. */
@@ -356,10 +371,17 @@ int orc_qp_solve(const orc_qp *qp, int iter_max, double tol, double *dx, double 
   const double thr0 = 0.1, mu0 = 0.1;
   res0 = 0.0;
   for (int i = 0; i < nb; i++) {
-    t_l[i] = fmax(du[i] - qp->lb[i], thr0);
-    t_u[i] = fmax(qp->ub[i] - du[i], thr0);
-    lam_l[i] = mu0 / t_l[i];
-    lam_u[i] = mu0 / t_u[i];
+    if (warm_eps > 0.0) {
+      t_l[i] = fmax(t_l_io[i], warm_eps);
+      t_u[i] = fmax(t_u_io[i], warm_eps);
+      lam_l[i] = fmax(lam_l[i], warm_eps);
+      lam_u[i] = fmax(lam_u[i], warm_eps);
+    } else {
+      t_l[i] = fmax(du[i] - qp->lb[i], thr0);
+      t_u[i] = fmax(qp->ub[i] - du[i], thr0);
+      lam_l[i] = mu0 / t_l[i];
+      lam_u[i] = mu0 / t_u[i];
+    }
     rbl0[i] = du[i] - qp->lb[i] - t_l[i];
     rbu0[i] = qp->ub[i] - du[i] - t_u[i];
     ru0[i] = -lam_l[i] + lam_u[i];
@@ -464,6 +486,11 @@ int orc_qp_solve(const orc_qp *qp, int iter_max, double tol, double *dx, double 
     for (int i = 0; i < (N + 1) * NX; i++) dx[i] += alpha * (xa[i] + xc[i]);
     rho *= (1.0 - alpha);
   }
+  if (t_l_io && t_u_io) {
+    memcpy(t_l_io, t_l, sizeof(double) * (size_t)nb);
+    memcpy(t_u_io, t_u, sizeof(double) * (size_t)nb);
+  }
+  if (ipm_converged) *ipm_converged = (status == ORC_SUCCESS);
 done:
   if (iters) *iters = it;
   free(buf);

@@ -30,6 +30,8 @@ int orc_solve(const orc_config *c, const double *x0, const double *yref, const d
   double *du = (double *)malloc(sizeof(double) * (size_t)N * NU);
   double *ll = (double *)malloc(sizeof(double) * (size_t)N * NU);
   double *lu = (double *)malloc(sizeof(double) * (size_t)N * NU);
+  double *tl = (double *)calloc((size_t)N * NU, sizeof(double));
+  double *tu = (double *)calloc((size_t)N * NU, sizeof(double));
   orc_qp *qp = orc_qp_alloc(N);
 
   if (*valid) { /* controller.py:419-424 : previous solution, NOT shifted; stage 0 x <- x0 (:416) */
@@ -43,11 +45,17 @@ int orc_solve(const orc_config *c, const double *x0, const double *yref, const d
 
   int status = ORC_SUCCESS;
   int tot_qp = 0, nsqp = 0, converged = 0;
+  int have_ipm = 0;       /* previous QP of this solve left a converged interior-point iterate */
+  double prev_step = 0.0; /* inf-norm of the previous SQP step */
   const int max_sqp = c->max_sqp_iter < 1 ? 1 : c->max_sqp_iter;
   while (nsqp < max_sqp) {
     orc_build_qp(c, xb, ub, yref, yref_e, qp);
     int qi = 0;
-    const int qs = orc_qp_solve(qp, c->qp_iter_max, c->ipm_tol, dx, du, ll, lu, &qi);
+    double weps = 0.0;
+    if (c->ipm_warm && have_ipm && prev_step <= ORC_WARM_STEP_MAX)
+      weps = fmin(fmax(ORC_WARM_KAPPA * prev_step, ORC_WARM_EPS_MIN), ORC_WARM_EPS_MAX);
+    const int qs = orc_qp_solve_warm(qp, c->qp_iter_max, c->ipm_tol, dx, du, ll, lu, tl, tu, weps,
+                                     &have_ipm, &qi);
     tot_qp += qi;
     nsqp++;
     /* UPSTREAM acados SQP_RTI: a QP that only hit its iteration cap is tolerated. */
@@ -68,6 +76,7 @@ int orc_solve(const orc_config *c, const double *x0, const double *yref, const d
       status = c->nan_status;
       break;
     }
+    prev_step = step;
     if (step <= c->sqp_tol) {
       converged = 1;
       break;
@@ -94,6 +103,8 @@ int orc_solve(const orc_config *c, const double *x0, const double *yref, const d
   free(du);
   free(ll);
   free(lu);
+  free(tl);
+  free(tu);
   return status;
 }
 

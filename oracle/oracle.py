@@ -33,6 +33,7 @@ class OrcConfig(C.Structure):
         ('w_max', C.c_double), ('integ_ns', C.c_int), ('integ_steps', C.c_int),
         ('cost_scale_dt', C.c_int), ('lm_scaled_by_dt', C.c_int), ('max_sqp_iter', C.c_int),
         ('sqp_tol', C.c_double), ('ipm_tol', C.c_double), ('nan_status', C.c_int),
+        ('ipm_warm', C.c_int),
     ]
 
 
@@ -125,6 +126,7 @@ def config_from_params(params: Dict[str, Dict[str, object]], **flags) -> OrcConf
     c.sqp_tol = float(flags.get('sqp_tol', 1e-8))
     c.ipm_tol = float(flags.get('ipm_tol', 1e-14))
     c.nan_status = int(flags.get('nan_status', 4))
+    c.ipm_warm = int(bool(flags.get('ipm_warm', s.get('ipm_warm_start', True))))
     return c
 
 

@@ -111,6 +111,7 @@ DevCfg<T> make_devcfg(const nmpc_config_t& c) {
   d.integ_steps = c.integ_steps;
   d.max_sqp_iter = c.max_sqp_iter;
   d.nan_status = c.nan_status;
+  d.ipm_warm = c.ipm_warm_start != 0;
   d.dt = (T)c.dt;
   d.h = (T)(c.dt / (double)c.integ_steps);
   const double sc = c.cost_scale_dt ? c.dt : 1.0;

@@ -17,6 +17,7 @@ constexpr int NZ = 17;  // per-stage variable order used on the device: z = [u(4
 template <typename T>
 struct DevCfg {
   int N, qp_iter_max, integ_steps, max_sqp_iter, nan_status;
+  bool ipm_warm;      // interior-point warm start between the QPs of one SQP run
   T dt, h;            // shooting interval and integrator sub-step
   T Wq[NX], Wr[NU];   // scaled stage weights (sc * W)
   T Qd[NX], Rd[NU];   // stage Hessian diagonals incl. LM

@@ -262,11 +262,15 @@ namespace nmpc {
 //           lam = mu0/t.  One step length for primal and dual, so the remaining linear residuals
 //           (box, u-stationarity) are rho = prod(1-alpha) times their initial values rbl0, rbu0,
 //           ru0 and every Newton right-hand side is built from those (no cancellation).
-// Returns the QP status; *iters = number of Riccati factorisations.
+//  warm_eps > 0 (QPs after the first of an SQP run, see solve_one): the slacks and multipliers
+//           the previous QP left in the workspace are the start instead, clipped to >= warm_eps.
+// Returns the QP status; *iters = number of Riccati factorisations; *ipm_conv = the interior-point
+// loop ran and met its tolerance (its iterate is a valid warm start for the next QP).
 template <typename T>
 __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
                                          const WsLayout& L, T* __restrict__ sm, int lane,
-                                         int* iters) {
+                                         T warm_eps, bool* ipm_conv, int* iters) {
+  *ipm_conv = false;
   const int N = c.N;
   const int nb = N * NU;
   const int nxv = (N + 1) * NX;
@@ -301,8 +305,14 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
   _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
     const T du = ws[L.du + i], lb = ws[L.lb + i], ub = ws[L.ubd + i];
     feas = feas && (du >= lb) && (du <= ub);
-    const T tl = fmax(du - lb, thr0), tu = fmax(ub - du, thr0);
-    const T ll = mu0 / tl, lu = mu0 / tu;
+    T tl = fmax(du - lb, thr0), tu = fmax(ub - du, thr0);
+    T ll = mu0 / tl, lu = mu0 / tu;
+    if (warm_eps > T(0)) {
+      tl = fmax(ws[L.tl + i], warm_eps);
+      tu = fmax(ws[L.tu + i], warm_eps);
+      ll = fmax(ws[L.ll + i], warm_eps);
+      lu = fmax(ws[L.lu + i], warm_eps);
+    }
     const T rbl = du - lb - tl, rbu = ub - du - tu, ru = -ll + lu;
     ws[L.tl + i] = tl;
     ws[L.tu + i] = tu;
@@ -510,6 +520,7 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
   __syncwarp();
   forward_sweep<T>(c, ws, L, sm, lane, true, false, true, true, L.kff, L.dx, L.du);
   *iters = it;
+  *ipm_conv = (status == ST_SUCCESS);
   return status;
 }
 
@@ -566,13 +577,20 @@ __device__ __forceinline__ void solve_one(const SolveArgs<T>& A, const WsLayout&
   int status = ST_SUCCESS;
   int tot_qp = 0, nsqp = 0;
   bool converged = false;
+  bool have_ipm = false;  // the previous QP of this solve left a converged interior-point iterate
+  T prev_step = T(0);
+  // FP32 cannot resolve slacks below ~1e-4 of the thrust scale
+  const T eps_min = sizeof(T) == 4 ? T(1e-4) : T(NMPC_WARM_EPS_MIN);
   const int max_sqp = c.max_sqp_iter < 1 ? 1 : c.max_sqp_iter;
   while (nsqp < max_sqp) {
     linearize<T, NS>(c, ws, L, lane);
     gradients(c, ws, L, yref, yref_e, lane);
     __syncwarp();
     int qi = 0;
-    const int qs = ipm_solve(c, ws, L, sm, lane, &qi);
+    T weps = T(0);
+    if (c.ipm_warm && have_ipm && prev_step <= T(NMPC_WARM_STEP_MAX))
+      weps = fmin(fmax(T(NMPC_WARM_KAPPA) * prev_step, eps_min), T(NMPC_WARM_EPS_MAX));
+    const int qs = ipm_solve(c, ws, L, sm, lane, weps, &have_ipm, &qi);
     tot_qp += qi;
     nsqp++;
     // acados SQP_RTI tolerates a QP that only hit its iteration cap
@@ -603,6 +621,7 @@ __device__ __forceinline__ void solve_one(const SolveArgs<T>& A, const WsLayout&
       break;
     }
     step = warp_max(step);
+    prev_step = step;
     if (step <= c.sqp_tol) {
       converged = true;
       break;

@@ -177,3 +177,38 @@ def test_abi_error_codes(params, built):
     assert lib.nmpc_batch(None) == -1
     assert b'invalid' in lib.nmpc_strerror(-1)
     assert lib.nmpc_destroy(h) == 0
+
+
+def test_sqp_ipm_warm_start_is_a_pure_speed_up(params, O):
+    """solver.ipm_warm_start (default on) only changes where the interior point of the 2nd, 3rd,
+    ... QP of an SQP run starts: every QP is still solved to the same tolerance, so the converged
+    iterate agrees with the cold-start run to the SQP tolerance (1e-8 step) and the statuses are
+    equal, with a third fewer Riccati factorisations.  Both variants match the oracle run with
+    the same flag (iteration counts included); RTI solves are untouched."""
+    from rotors_mpc_controller_b200 import BatchedPositionNMPC
+    B = 384
+    rng = np.random.default_rng(21)
+    x0 = random_states(rng, B)
+    out = {}
+    for warm in (False, True):
+        p = copy.deepcopy(params)
+        p['solver'].update(max_sqp_iter=50, sqp_tol=1e-8, ipm_warm_start=warm)
+        ctl = BatchedPositionNMPC(p, batch=B)
+        if not warm:
+            yref, yref_e = setpoint_refs(np.random.default_rng(22), x0, 20, ctl.hover_thrust)
+        u0, st = ctl.solve(x0, yref, yref_e)
+        s = ctl.stats()
+        ob = O.OracleBatch(O.config_from_params(p, max_sqp_iter=50, sqp_tol=1e-8), B)
+        ur, sr, _, _ = ob.solve(x0, yref, yref_e)
+        assert np.array_equal(st, sr)
+        assert np.max(np.abs(u0 - ur)) < 1e-7             # two SQP runs stopping at step <= 1e-8
+        same = s['sqp_iters'] > 0
+        assert np.mean(s['qp_iters'] == ob.qp_iters) > 0.98   # same path up to rounding ties
+        out[warm] = (u0.copy(), st.copy(), s['qp_iters'].copy(), s['sqp_iters'].copy())
+        ctl.close()
+        assert same.all()
+    assert np.array_equal(out[True][1], out[False][1]) and np.all(out[True][1] == 0)
+    assert np.max(np.abs(out[True][0] - out[False][0])) < 1e-7
+    assert out[True][2].sum() < 0.75 * out[False][2].sum()
+    assert out[True][2].max() < 0.75 * out[False][2].max()
+    assert np.mean(out[True][3] == out[False][3]) > 0.95      # same number of SQP iterations
