@@ -317,8 +317,7 @@ int orc_qp_solve(const orc_qp *qp, int iter_max, double tol, double *dx, double 
  * of one SQP run, see orc_solve): with warm_eps > 0 the loop starts from the previous QP's slacks
  * (t_l_io, t_u_io) and multipliers (lam_l, lam_u), pushed away from the boundary,
  *     t = max(t_prev, eps),  lam = max(lam_prev, eps),
- * instead of t = max(slack, 0.1), lam = 0.1 / t.  Phase 0 is unchanged, so the primal start and
- * the residual bookkeeping (rho) are the same.  On return t_l_io / t_u_io (when given) hold the
+ * instead of t = max(slack, 0.1), lam = 0.1 / t, and phase 0 is skipped (see below).  On return t_l_io / t_u_io (when given) hold the
  * slacks of the final iterate and *ipm_converged tells whether the interior-point loop ran and
  * met its tolerance (only then is the iterate a valid warm start for the next QP). */
 int orc_qp_solve_warm(const orc_qp *qp, int iter_max, double tol, double *dx, double *du,
@@ -351,12 +350,22 @@ int orc_qp_solve_warm(const orc_qp *qp, int iter_max, double tol, double *dx, do
     status = ORC_QP_FAILURE;
     goto done;
   }
-  if (riccati_factor_solve(qp, 1.0, qp->R, qp->r, &ws, dx, du)) {
-    status = ORC_QP_FAILURE;
-    goto done;
+  /* A warm-started QP skips phase 0 (its bounds were active a moment ago): the loop starts at
+   * dz = 0, where the dynamics and x-stationarity residuals are the plain data b and q; they
+   * shrink with rho like the others and enter every Riccati solve as (rho b, rho q). */
+  const int skip0 = warm_eps > 0.0;
+  const double rq = skip0 ? 1.0 : 0.0;
+  if (skip0) {
+    for (int i = 0; i < nb; i++) du[i] = 0.0;
+    for (int i = 0; i < (N + 1) * NX; i++) dx[i] = 0.0;
+  } else {
+    if (riccati_factor_solve(qp, 1.0, qp->R, qp->r, &ws, dx, du)) {
+      status = ORC_QP_FAILURE;
+      goto done;
+    }
+    it = 1; /* iterations are counted in Riccati factorisations */
   }
-  it = 1; /* iterations are counted in Riccati factorisations */
-  {
+  if (!skip0) {
     int feasible = 1;
     for (int i = 0; i < nb; i++)
       if (!(du[i] >= qp->lb[i] && du[i] <= qp->ub[i])) feasible = 0;
@@ -384,11 +393,15 @@ int orc_qp_solve_warm(const orc_qp *qp, int iter_max, double tol, double *dx, do
     }
     rbl0[i] = du[i] - qp->lb[i] - t_l[i];
     rbu0[i] = qp->ub[i] - du[i] - t_u[i];
-    ru0[i] = -lam_l[i] + lam_u[i];
+    ru0[i] = -lam_l[i] + lam_u[i] + rq * qp->r[i];
     res0 = fmax(res0, fmax(fabs(rbl0[i]), fabs(rbu0[i])));
     res0 = fmax(res0, fabs(ru0[i]));
   }
   double rho = 1.0;
+  if (skip0) {
+    for (int i = 0; i < N * NX; i++) res0 = fmax(res0, fabs(qp->b[i]));
+    for (int i = 0; i < (N + 1) * NX; i++) res0 = fmax(res0, fabs(qp->q[i]));
+  }
 
   for (; it < iter_max; it++) {
     double mu = 0.0;
@@ -408,7 +421,7 @@ int orc_qp_solve_warm(const orc_qp *qp, int iter_max, double tol, double *dx, do
       Rt[i] = qp->R[i] + dl + dw;
       rt[i] = rho * ru0[i] + dl * (rho * rbl0[i]) + lam_l[i] - dw * (rho * rbu0[i]) - lam_u[i];
     }
-    if (riccati_factor_solve(qp, 0.0, Rt, rt, &ws, xa, ua)) {
+    if (riccati_factor_solve(qp, rq * rho, Rt, rt, &ws, xa, ua)) {
       status = ORC_QP_FAILURE;
       break;
     }

@@ -37,7 +37,7 @@ struct WsLayout {
 
 // One record per stage keeps what the sweeps stream together contiguous (one 16-byte-chunked
 // cp.async range per stage): M_k at L.M + k*REC, K_k at L.K + k*REC.
-constexpr int M_LD = NZ + 1;             // 18: row stride of M_k (rows start 16-byte aligned)
+constexpr int M_LD = NZ + 1;             // 18: row [B_k | A_k | b_k] (rows start 16-byte aligned)
 constexpr int REC_K = NX * M_LD;         // 234: offset of K_k inside a record
 constexpr int REC = REC_K + NU * NX;     // 286
 
@@ -51,7 +51,7 @@ __host__ __device__ inline WsLayout make_layout(int N) {
     return r;
   };
   const int nx = (N + 1) * NX, nu = N * NU;
-  L.M = take(N * REC);  // stage records [M_k (13 rows of 17+1) | K_k (4x13)], REC elements each
+  L.M = take(N * REC);  // stage records [M_k | b_k (13 rows of 17+1) | K_k (4x13)], REC each
   L.K = L.M + REC_K;
   L.Qi = take(N * 16);
   L.kff = take(nu);
@@ -215,14 +215,18 @@ __device__ __forceinline__ void linearize(const DevCfg<T>& c, T* __restrict__ ws
       su[i] = (lane == i) ? T(1) : T(0);
     }
     erk_column<T, NS>(c, x, u, s, su);
-    if (lane < M_LD) {  // lane 17 zeroes the row padding
+    if (lane < NZ) {
 #pragma unroll
-      for (int i = 0; i < NX; i++) M[k * REC + i * M_LD + lane] = (lane < NZ) ? s[i] : T(0);
+      for (int i = 0; i < NX; i++) M[k * REC + i * M_LD + lane] = s[i];
     }
     T xl = x[0];  // every lane holds the same nominal x; lane i writes component i
 #pragma unroll
     for (int i = 1; i < NX; i++) xl = (lane == i) ? x[i] : xl;
-    if (lane < NX) bv[k * NX + lane] = xl - xb[(k + 1) * NX + lane];
+    if (lane < NX) {  // defect; a copy rides in column 17 of M_k's rows (staged with the tile)
+      const T bk = xl - xb[(k + 1) * NX + lane];
+      bv[k * NX + lane] = bk;
+      M[k * REC + lane * M_LD + NZ] = bk;
+    }
   }
 }
 
@@ -263,7 +267,8 @@ namespace nmpc {
 //           (box, u-stationarity) are rho = prod(1-alpha) times their initial values rbl0, rbu0,
 //           ru0 and every Newton right-hand side is built from those (no cancellation).
 //  warm_eps > 0 (QPs after the first of an SQP run, see solve_one): the slacks and multipliers
-//           the previous QP left in the workspace are the start instead, clipped to >= warm_eps.
+//           the previous QP left in the workspace are the start instead, clipped to >= warm_eps,
+//           and phase 0 is skipped (start at dz = 0, residuals b and q scaled by rho as well).
 // Returns the QP status; *iters = number of Riccati factorisations; *ipm_conv = the interior-point
 // loop ran and met its tolerance (its iterate is a valid warm start for the next QP).
 template <typename T>
@@ -277,43 +282,65 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
   const T thr0 = T(0.1), mu0 = T(0.1);
   int it = 0;
 
+  // A warm-started QP skips phase 0 (its bounds were active a moment ago): the loop starts at
+  // dz = 0, where the dynamics and x-stationarity residuals are the plain data b and q; they
+  // shrink with rho like the box and u-stationarity residuals and enter every Riccati solve as
+  // (rho b, rho q).
+  const bool skip0 = warm_eps > T(0);
+
   // finite check of the QP data (NaN state / reference -> QP failure, status 4)
+  T res0 = T(0);
   {
     bool fin = true;
     _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
       fin = fin && finite_(ws[L.r + i]) && finite_(ws[L.lb + i]) && finite_(ws[L.ubd + i]);
       ws[L.rt + i] = ws[L.r + i];
     }
-    _Pragma("unroll 3") for (int i = lane; i < nxv; i += 32) fin = fin && finite_(ws[L.q + i]);
-    _Pragma("unroll 3") for (int i = lane; i < N * NX; i += 32) fin = fin && finite_(ws[L.b + i]);
+    _Pragma("unroll 3") for (int i = lane; i < nxv; i += 32) {
+      const T v = ws[L.q + i];
+      fin = fin && finite_(v);
+      res0 = fmax(res0, fabs(v));
+    }
+    _Pragma("unroll 3") for (int i = lane; i < N * NX; i += 32) {
+      const T v = ws[L.b + i];
+      fin = fin && finite_(v);
+      res0 = fmax(res0, fabs(v));
+    }
     if (!__all_sync(FULL, fin)) {
       *iters = 0;
       return ST_QPFAIL;
     }
   }
   __syncwarp();
-  bool ok = factor_sweep(c, ws, L, sm, lane, true);
-  it = 1;
-  if (!ok) {
-    *iters = it;
-    return ST_QPFAIL;
+  if (!skip0) {
+    res0 = T(0);  // b and q are met exactly by the phase-0 point
+    const bool ok0 = factor_sweep(c, ws, L, sm, lane, T(1));
+    it = 1;
+    if (!ok0) {
+      *iters = it;
+      return ST_QPFAIL;
+    }
+    forward_sweep<T>(c, ws, L, sm, lane, T(1), false, true, false, L.kff, L.dx, L.du);
   }
-  forward_sweep<T>(c, ws, L, sm, lane, true, false, true, false, L.kff, L.dx, L.du);
   // box check + interior-point start
-  bool feas = true;
-  T res0 = T(0);
+  bool feas = !skip0;
   _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
-    const T du = ws[L.du + i], lb = ws[L.lb + i], ub = ws[L.ubd + i];
+    const T du = skip0 ? T(0) : ws[L.du + i];
+    const T lb = ws[L.lb + i], ub = ws[L.ubd + i];
     feas = feas && (du >= lb) && (du <= ub);
     T tl = fmax(du - lb, thr0), tu = fmax(ub - du, thr0);
     T ll = mu0 / tl, lu = mu0 / tu;
-    if (warm_eps > T(0)) {
+    T ru = T(0);
+    if (skip0) {
       tl = fmax(ws[L.tl + i], warm_eps);
       tu = fmax(ws[L.tu + i], warm_eps);
       ll = fmax(ws[L.ll + i], warm_eps);
       lu = fmax(ws[L.lu + i], warm_eps);
+      ru = ws[L.r + i];
+      ws[L.du + i] = T(0);
     }
-    const T rbl = du - lb - tl, rbu = ub - du - tu, ru = -ll + lu;
+    ru += -ll + lu;
+    const T rbl = du - lb - tl, rbu = ub - du - tu;
     ws[L.tl + i] = tl;
     ws[L.tu + i] = tu;
     ws[L.ll + i] = ll;
@@ -381,14 +408,15 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
       break;
     }
     __syncwarp();
-    ok = factor_sweep(c, ws, L, sm, lane, false);
+    const T rq = skip0 ? rho : T(0);
+    const bool ok = factor_sweep(c, ws, L, sm, lane, rq);
     if (!ok) {
       // FP32 precision floor: once the complementarity is below 1e-6 a lost pivot means the
       // barrier Hessian can no longer be resolved in single precision -> keep the iterate
       status = (sizeof(T) == 4 && mu <= T(1e-6)) ? ST_SUCCESS : ST_QPFAIL;
       break;
     }
-    forward_sweep<T>(c, ws, L, sm, lane, false, false, false, false, L.kff, L.xa, L.ua);
+    forward_sweep<T>(c, ws, L, sm, lane, rq, false, false, false, L.kff, L.xa, L.ua);
     // affine step length (division-free ratio test: the running minimum is kept as a fraction
     // an/ad and candidates are compared by cross-multiplication)
     T an = T(1), ad = T(1);
@@ -442,7 +470,7 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
     __syncwarp();
     // corrector increment (vector-only re-solve), accumulated onto the predictor direction
     delta_backward(c, ws, L, sm, lane);
-    forward_sweep<T>(c, ws, L, sm, lane, false, true, false, false, L.kffd, L.xa, L.ua);
+    forward_sweep<T>(c, ws, L, sm, lane, T(0), true, false, false, L.kffd, L.xa, L.ua);
     T bn = T(2), bd = T(1);  // ratios >= 2 cannot bind: alpha = min(1, tau * ratio), tau >= 0.995
     bool fin = true;         // NaN anywhere must surface: comparisons drop NaNs, so test explicitly
     NMPC_ROWS({
@@ -518,7 +546,7 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
   // The state direction is only needed once: roll the linearised dynamics out for the final
   // input direction, dx_{k+1} = A_k dx_k + B_k du_k + b_k (instead of updating dx every iteration).
   __syncwarp();
-  forward_sweep<T>(c, ws, L, sm, lane, true, false, true, true, L.kff, L.dx, L.du);
+  forward_sweep<T>(c, ws, L, sm, lane, T(1), false, true, true, L.kff, L.dx, L.du);
   *iters = it;
   *ipm_conv = (status == ST_SUCCESS);
   return status;
