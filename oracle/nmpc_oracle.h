@@ -69,10 +69,18 @@ typedef struct {
 /* Warm start between the QPs of one SQP run: used when the previous QP's interior-point loop
  * converged and the previous SQP step was <= ORC_WARM_STEP_MAX (the active set is settling);
  * the iterate is clipped to eps = clamp(ORC_WARM_KAPPA * step, ORC_WARM_EPS_MIN, ORC_WARM_EPS_MAX). */
+#ifndef ORC_WARM_KAPPA
 #define ORC_WARM_KAPPA 0.1
+#endif
+#ifndef ORC_WARM_STEP_MAX
 #define ORC_WARM_STEP_MAX 0.3
+#endif
+#ifndef ORC_WARM_EPS_MIN
 #define ORC_WARM_EPS_MIN 1e-8
+#endif
+#ifndef ORC_WARM_EPS_MAX
 #define ORC_WARM_EPS_MAX 0.1
+#endif
 
 /* continuous model, controller.py:267-355 */
 void orc_f(const orc_config *c, const double *x, const double *u, double *f);
