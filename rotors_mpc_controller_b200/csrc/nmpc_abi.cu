@@ -34,6 +34,8 @@ __global__ void __launch_bounds__(WARPS * 32, MIN_CTAS)
   T* sm = reinterpret_cast<T*>(smem_raw) + warp * smem_elems_per_warp();
   const int slot = blockIdx.x * WARPS + warp;
   T* ws = A.ws + (size_t)slot * L.total;
+  init_position_columns(A.cfg.N, ws, L, lane);  // constant columns e_a of every A_k
+  __syncwarp();
   // dynamic work queue: iteration counts differ per problem, so problems are handed out one
   // at a time instead of in a fixed stride
   for (;;) {

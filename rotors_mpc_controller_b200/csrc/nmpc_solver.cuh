@@ -193,8 +193,21 @@ __device__ __forceinline__ bool spd4_inverse(const T (&G)[4][4], T (&Gi)[4][4]) 
 }
 
 // ------------------------------------------------------------------ K1: linearisation
-// For every stage: ERK + forward sensitivities -> M_k = [B_k | A_k] (row-major 13 x 17 in the
-// workspace, so that lane j reads/writes column j coalesced) and the defect b_k.
+// For every stage: ERK + forward sensitivities -> M_k = [B_k | A_k] (row-major 13 x 18 in the
+// stage record) and the defect b_k.  Stages are independent (multiple shooting) and nothing in the
+// model depends on the position, so column p_a of A_k is the constant e_a: only the 14 columns
+// u, v, q, w are integrated, one per lane, and the two half-warps take two stages at a time.
+// The position columns are written once per launch (init_position_columns).
+template <typename T>
+__device__ __forceinline__ void init_position_columns(int N, T* __restrict__ ws,
+                                                      const WsLayout& L, int lane) {
+  _Pragma("unroll 1") for (int idx = lane; idx < N * NX * 3; idx += 32) {
+    const int k = idx / (NX * 3), r = idx - k * (NX * 3);
+    const int i = r / 3, a = r - 3 * i;
+    ws[L.M + k * REC + i * M_LD + NU + a] = (i == a) ? T(1) : T(0);
+  }
+}
+
 template <typename T, int NS>
 __device__ __forceinline__ void linearize(const DevCfg<T>& c, T* __restrict__ ws,
                                           const WsLayout& L, int lane) {
@@ -202,30 +215,36 @@ __device__ __forceinline__ void linearize(const DevCfg<T>& c, T* __restrict__ ws
   const T* ub = ws + L.ub;
   T* M = ws + L.M;
   T* bv = ws + L.b;
-  for (int k = 0; k < c.N; k++) {
+  const int h = lane >> 4, cl = lane & 15;
+  const bool ccol = cl < NZ - 3;              // 14 integrated columns per stage
+  const int sx = cl - 1;                      // state seeded by lanes 4..13: v, q, w = 3..12
+  const int zc = cl < NU ? cl : cl + 3;       // column of M_k = [B | A]
+  for (int k0 = 0; k0 < c.N; k0 += 2) {
+    const bool live = k0 + h < c.N;           // odd horizons: the upper half idles on the last pass
+    const int k = live ? k0 + h : c.N - 1;
     T x[NX], u[NU], s[NX], su[NU];
 #pragma unroll
     for (int i = 0; i < NX; i++) {
       x[i] = xb[k * NX + i];
-      s[i] = (lane - NU == i) ? T(1) : T(0);
+      s[i] = (cl >= NU && sx == i) ? T(1) : T(0);
     }
 #pragma unroll
     for (int i = 0; i < NU; i++) {
       u[i] = ub[k * NU + i];
-      su[i] = (lane == i) ? T(1) : T(0);
+      su[i] = (cl == i) ? T(1) : T(0);
     }
     erk_column<T, NS>(c, x, u, s, su);
-    if (lane < NZ) {
+    if (live && ccol) {
 #pragma unroll
-      for (int i = 0; i < NX; i++) M[k * REC + i * M_LD + lane] = s[i];
+      for (int i = 0; i < NX; i++) M[k * REC + i * M_LD + zc] = s[i];
     }
-    T xl = x[0];  // every lane holds the same nominal x; lane i writes component i
+    T xl = x[0];  // every lane of a half holds the same nominal x; lane i writes component i
 #pragma unroll
-    for (int i = 1; i < NX; i++) xl = (lane == i) ? x[i] : xl;
-    if (lane < NX) {  // defect; a copy rides in column 17 of M_k's rows (staged with the tile)
-      const T bk = xl - xb[(k + 1) * NX + lane];
-      bv[k * NX + lane] = bk;
-      M[k * REC + lane * M_LD + NZ] = bk;
+    for (int i = 1; i < NX; i++) xl = (cl == i) ? x[i] : xl;
+    if (live && cl < NX) {  // defect; a copy rides in column 17 of M_k's rows (staged with the tile)
+      const T bk = xl - xb[(k + 1) * NX + cl];
+      bv[k * NX + cl] = bk;
+      M[k * REC + cl * M_LD + NZ] = bk;
     }
   }
 }
