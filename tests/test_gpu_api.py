@@ -212,3 +212,25 @@ def test_sqp_ipm_warm_start_is_a_pure_speed_up(params, O):
     assert out[True][2].sum() < 0.75 * out[False][2].sum()
     assert out[True][2].max() < 0.75 * out[False][2].max()
     assert np.mean(out[True][3] == out[False][3]) > 0.95      # same number of SQP iterations
+
+
+def test_fp32_sqp_with_warm_start(params):
+    """FP32 variant in SQP mode (tolerance an FP32 iterate can reach): statuses equal to the FP64
+    run, u0 within north_star's 1e-3 relative, warm start does not cost accuracy."""
+    from rotors_mpc_controller_b200 import BatchedPositionNMPC
+    B = 2048
+    x0 = random_states(np.random.default_rng(0), B)
+    res = {}
+    for prec in ('f64', 'f32'):
+        p = copy.deepcopy(params)
+        p['solver'].update(max_sqp_iter=30, sqp_tol=1e-4, precision=prec)
+        ctl = BatchedPositionNMPC(p, batch=B)
+        if not res:
+            yref, yref_e = setpoint_refs(np.random.default_rng(1), x0, 20, ctl.hover_thrust)
+        u0, st = ctl.solve(x0, yref, yref_e)
+        res[prec] = (u0.copy(), st.copy(), ctl.stats()['qp_iters'].mean())
+        ctl.close()
+    assert np.array_equal(res['f32'][1], res['f64'][1]) and np.all(res['f64'][1] == 0)
+    rel = np.abs(res['f32'][0] - res['f64'][0]).max() / np.abs(res['f64'][0]).max()
+    assert rel < 1e-3
+    assert res['f32'][2] < 1.2 * res['f64'][2]        # no extra interior-point iterations
