@@ -25,13 +25,16 @@ namespace {
 #ifndef NMPC_MAXNREG
 #define NMPC_MAXNREG 152
 #endif
+#ifndef NMPC_MAXNREG_F32
+#define NMPC_MAXNREG_F32 128
+#endif
 constexpr int WARPS = NMPC_WARPS;  // warps (= problems in flight) per CTA
 
 constexpr int smem_elems_per_warp() { return (SmemLayout::total + 3) & ~3; }
 
 // ---------------------------------------------------------------- kernels
 template <typename T, int NS>
-__global__ void __maxnreg__(NMPC_MAXNREG)
+__global__ void __maxnreg__(sizeof(T) == 4 ? NMPC_MAXNREG_F32 : NMPC_MAXNREG)
     nmpc_solve_kernel(const __grid_constant__ SolveArgs<T> A, const __grid_constant__ WsLayout L,
                       int* __restrict__ work_counter) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
