@@ -16,14 +16,16 @@ using namespace nmpc;
 
 namespace {
 
-// One warp per CTA (warps never synchronise with each other) and a 152-register cap: 13 problems
-// in flight per SM.  The solver is latency bound, so resident warps are what buys throughput:
-// 12 warps at 168 registers are 7 % slower, 14 warps at 144 registers spill and gain only 3 %.
+// One warp per CTA (warps never synchronise with each other).  The register file is partitioned
+// per scheduler (16 K registers each): 3 warps per scheduler = 12 problems in flight per SM fit up
+// to 170 registers, 4 per scheduler need <= 128 (FP32 kernels do, FP64 ones spill in the sweeps and
+// lose more than the extra warps bring).  The FP64 cap is set a little below what ptxas would take
+// (156): the 160-register schedule measures 4-5 % faster than the unconstrained one.
 #ifndef NMPC_WARPS
 #define NMPC_WARPS 1
 #endif
 #ifndef NMPC_MAXNREG
-#define NMPC_MAXNREG 152
+#define NMPC_MAXNREG 160
 #endif
 #ifndef NMPC_MAXNREG_F32
 #define NMPC_MAXNREG_F32 128
