@@ -431,6 +431,32 @@ def extras(params, dev):
                               'mean_factorisations': s['qp_iters'] / (B * steps),
                               'failed_solves': s['failed_solves']}
     ctl.close()
+    # configs[0]: ONE vehicle through the reference's own call surface (PositionNMPC.solve with
+    # state / reference dicts, host buffers), closed loop hover (0,0,1) -> set-point (2,0,1.5)
+    from rotors_mpc_controller_b200 import PositionNMPC, ReferenceGenerator
+    p1 = copy.deepcopy(params)
+    p1['solver']['max_sqp_iter'] = 1
+    one = PositionNMPC(p1, device=dev.index)
+    ref = ReferenceGenerator(p1['reference'])
+    ref.update_hover_thrust(one.hover_thrust)
+    ref.set_target(position=[2.0, 0.0, 1.5], yaw=0.0)
+    horizon = ref.build_horizon(one.horizon, one.dt)
+    plant = ClosedLoop(one, Plant(dt=one.dt, substeps=5))     # nominal RK4 plant (device kernel)
+    x = np.array([0, 0, 1, 0, 0, 0, 1, 0, 0, 0, 0, 0, 0], float)
+    plant.reset(x[None])
+    lat = []
+    for step in range(120):
+        state = {'position': x[0:3], 'velocity': x[3:6], 'quaternion': x[6:10], 'body_rates': x[10:13]}
+        t0 = time.perf_counter()
+        u0, status = one.solve(state, horizon)
+        lat.append(time.perf_counter() - t0)
+        thrust, _ = one.command()
+        x = plant.plant_step(thrust[None]).cpu().numpy()[0]
+    out['single_vehicle_rti'] = {
+        'call': 'PositionNMPC.solve(state, reference) + command(), batch 1, host buffers',
+        'p50_latency_us': float(np.median(lat[20:]) * 1e6), 'p99_latency_us': float(np.percentile(lat[20:], 99) * 1e6),
+        'final_position': [float(v) for v in x[0:3]], 'last_status': int(status)}
+    one.close()
     return out
 
 
