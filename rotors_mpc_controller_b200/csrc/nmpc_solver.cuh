@@ -29,7 +29,7 @@ enum : int { ST_SUCCESS = 0, ST_NAN = 1, ST_MAXITER = 2, ST_MINSTEP = 3, ST_QPFA
 struct WsLayout {
   int N;
   int M, K, Qi, kff, kffd;
-  int xb, q, b, dx, xa;                                            // x-type vectors
+  int xb, q, b, dx;                                                // x-type vectors
   int ub, r, lb, ubd, du, ua, tl, tu, ll, lu, rbl0, rbu0, ru0;    // u-type vectors
   int dtl, dtu, dll, dlu, Rt, rt, dr, itl, itu;
   int total;
@@ -60,7 +60,6 @@ __host__ __device__ inline WsLayout make_layout(int N) {
   L.q = take(nx);
   L.b = take(nx);
   L.dx = take(nx);
-  L.xa = take(nx);
   L.ub = take(nu);
   L.r = take(nu);
   L.lb = take(nu);
@@ -98,8 +97,7 @@ struct SmemLayout {
   static constexpr int wv = p + 14;              // 13 (+1)
   static constexpr int xA = wv + 14;             // 13 (+1) forward-sweep state, ping
   static constexpr int xB = xA + 14;             // pong
-  static constexpr int u = xB + 14;              // 4
-  static constexpr int total = u + 4;            // 990 elements
+  static constexpr int total = xB + 14;          // 986 elements
 };
 
 template <typename T>
@@ -142,54 +140,6 @@ __device__ __forceinline__ void ratio_min(T& num, T& den, T n, T d) {
 template <typename T>
 __device__ __forceinline__ bool finite_(T v) {
   return (v - v) == T(0);
-}
-
-// Inverse of a symmetric positive definite 4x4 (lower triangle of G used) via Cholesky.
-// Executed redundantly by every lane.  Returns false on a non-positive / NaN pivot.
-template <typename T>
-__device__ __forceinline__ bool spd4_inverse(const T (&G)[4][4], T (&Gi)[4][4]) {
-  T L[4][4], Li[4][4];
-  bool ok = true;
-#pragma unroll
-  for (int j = 0; j < 4; j++) {
-    T d = G[j][j];
-#pragma unroll
-    for (int k = 0; k < j; k++) d -= L[j][k] * L[j][k];
-    ok = ok && (d > T(0));
-    const T ljj = sqrt(d);
-    const T inv = T(1) / ljj;
-    L[j][j] = ljj;
-    Li[j][j] = inv;
-#pragma unroll
-    for (int i = j + 1; i < 4; i++) {
-      T s = G[i][j];
-#pragma unroll
-      for (int k = 0; k < j; k++) s -= L[i][k] * L[j][k];
-      L[i][j] = s * inv;
-    }
-  }
-#pragma unroll
-  for (int j = 0; j < 4; j++) {
-#pragma unroll
-    for (int i = j + 1; i < 4; i++) {
-      T s = T(0);
-#pragma unroll
-      for (int k = j; k < i; k++) s -= L[i][k] * Li[k][j];
-      Li[i][j] = s * Li[i][i];
-    }
-  }
-#pragma unroll
-  for (int i = 0; i < 4; i++) {
-#pragma unroll
-    for (int j = 0; j <= i; j++) {
-      T s = T(0);
-#pragma unroll
-      for (int k = i; k < 4; k++) s += Li[k][i] * Li[k][j];
-      Gi[i][j] = s;
-      Gi[j][i] = s;
-    }
-  }
-  return ok;
 }
 
 // ------------------------------------------------------------------ K1: linearisation
@@ -435,7 +385,7 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
       status = (sizeof(T) == 4 && mu <= T(1e-6)) ? ST_SUCCESS : ST_QPFAIL;
       break;
     }
-    forward_sweep<T>(c, ws, L, sm, lane, rq, false, false, false, L.kff, L.xa, L.ua);
+    forward_sweep<T>(c, ws, L, sm, lane, rq, false, false, false, L.kff, L.dx, L.ua);   // wx = false: no state output
     // affine step length (division-free ratio test: the running minimum is kept as a fraction
     // an/ad and candidates are compared by cross-multiplication)
     T an = T(1), ad = T(1);
@@ -489,7 +439,7 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
     __syncwarp();
     // corrector increment (vector-only re-solve), accumulated onto the predictor direction
     delta_backward(c, ws, L, sm, lane);
-    forward_sweep<T>(c, ws, L, sm, lane, T(0), true, false, false, L.kffd, L.xa, L.ua);
+    forward_sweep<T>(c, ws, L, sm, lane, T(0), true, false, false, L.kffd, L.dx, L.ua);
     T bn = T(2), bd = T(1);  // ratios >= 2 cannot bind: alpha = min(1, tau * ratio), tau >= 0.995
     bool fin = true;         // NaN anywhere must surface: comparisons drop NaNs, so test explicitly
     NMPC_ROWS({
