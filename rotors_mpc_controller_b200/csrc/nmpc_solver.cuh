@@ -160,9 +160,22 @@ __device__ __forceinline__ void init_position_columns(int N, T* __restrict__ ws,
 
 template <typename T, int NS>
 __device__ __forceinline__ void linearize(const DevCfg<T>& c, T* __restrict__ ws,
-                                          const WsLayout& L, int lane) {
+                                          const WsLayout& L, T* __restrict__ sm, int lane) {
+  // The iterate is read stage by stage below (17 broadcast loads per pass, each pass would wait
+  // for L2): when it fits the (idle) stage buffers it is copied to shared memory once, with all
+  // loads in flight together.
+  const int nxv = (c.N + 1) * NX, nuv = c.N * NU;
+  const bool staged = nxv + nuv <= SmemLayout::K - SmemLayout::M;
   const T* xb = ws + L.xb;
   const T* ub = ws + L.ub;
+  if (staged) {
+    T* sx = sm + SmemLayout::M;
+    _Pragma("unroll 3") for (int i = lane; i < nxv; i += 32) sx[i] = xb[i];
+    _Pragma("unroll 3") for (int i = lane; i < nuv; i += 32) sx[nxv + i] = ub[i];
+    xb = sx;
+    ub = sx + nxv;
+    __syncwarp();
+  }
   T* M = ws + L.M;
   T* bv = ws + L.b;
   const int h = lane >> 4, cl = lane & 15;
@@ -580,7 +593,7 @@ __device__ __forceinline__ void solve_one(const SolveArgs<T>& A, const WsLayout&
   const T eps_min = sizeof(T) == 4 ? T(1e-4) : T(NMPC_WARM_EPS_MIN);
   const int max_sqp = c.max_sqp_iter < 1 ? 1 : c.max_sqp_iter;
   while (nsqp < max_sqp) {
-    linearize<T, NS>(c, ws, L, lane);
+    linearize<T, NS>(c, ws, L, sm, lane);
     gradients(c, ws, L, yref, yref_e, lane);
     __syncwarp();
     int qi = 0;
