@@ -89,15 +89,15 @@ __host__ __device__ inline WsLayout make_layout(int N) {
 // Per-warp shared-memory tile (elements of T).
 constexpr int SP_LD = 14;  // padded leading dimension of P and K rows (16-byte aligned rows)
 struct SmemLayout {
-  static constexpr int P = 0;                    // 13 x 14 cost-to-go
-  static constexpr int M = P + NX * SP_LD;       // stage buffers of the sweeps (cp.async targets):
+  static constexpr int P = 0;                    // 13 x 14 cost-to-go + a zero row (dummy W row)
+  static constexpr int M = P + (NX + 1) * SP_LD; // stage buffers of the sweeps (cp.async targets):
                                                  //   factor: 2 x 234 + 224, forward: 2 x 286
   static constexpr int K = M + 692;              // 4 x 14
   static constexpr int p = K + NU * SP_LD;       // 13 (+1)
   static constexpr int wv = p + 14;              // 13 (+1)
   static constexpr int xA = wv + 14;             // 13 (+1) forward-sweep state, ping
   static constexpr int xB = xA + 14;             // pong
-  static constexpr int total = xB + 14;          // 986 elements
+  static constexpr int total = xB + 14;          // 1000 elements
 };
 
 template <typename T>
