@@ -32,7 +32,7 @@ namespace {
 #endif
 constexpr int WARPS = NMPC_WARPS;  // warps (= problems in flight) per CTA
 
-constexpr int smem_elems_per_warp() { return (SmemLayout::total + 3) & ~3; }
+constexpr int smem_elems_per_warp() { return smem_tile_elems(); }
 
 // ---------------------------------------------------------------- kernels
 template <typename T, int NS>
@@ -42,6 +42,10 @@ __global__ void __maxnreg__(sizeof(T) == 4 ? NMPC_MAXNREG_F32 : NMPC_MAXNREG)
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   T* sm = reinterpret_cast<T*>(smem_raw) + warp * smem_elems_per_warp();
+  if (A.stage && lane == 0) {  // mbarrier of the TMA input staging + its phase parity
+    reinterpret_cast<unsigned*>(sm + SmemLayout::bar)[2] = 0u;
+    mbar_init(sm + SmemLayout::bar);
+  }
   const int slot = blockIdx.x * WARPS + warp;
   T* ws = A.ws + (size_t)slot * L.total;
   init_position_columns(A.cfg.N, ws, L, lane);  // constant columns e_a of every A_k
@@ -165,6 +169,7 @@ DevCfg<T> make_devcfg(const nmpc_config_t& c) {
 struct nmpc_handle {
   nmpc_config_t cfg;
   int batch, device, sm_count, grid, nslots, launches;
+  int stage_bytes;  // bytes of inputs the solve kernel stages by TMA per problem (0: direct loads)
   WsLayout L;
   size_t ws_bytes;
   void* ws;
@@ -222,8 +227,15 @@ static int configure_kernel(nmpc_handle* h, size_t smem) {
 }
 
 template <typename T>
+static size_t solve_smem_bytes(const nmpc_handle* h) {
+  return (size_t)WARPS * smem_elems_per_warp() * sizeof(T);
+}
+
+template <typename T>
 static int configure_T(nmpc_handle* h) {
-  const size_t smem = (size_t)WARPS * smem_elems_per_warp() * sizeof(T);
+  h->stage_bytes = make_stage_layout(h->cfg.N, (int)sizeof(T)).total;
+  if (getenv("NMPC_B200_NO_TMA")) h->stage_bytes = 0;  // A/B knob: direct loads of the inputs
+  const size_t smem = solve_smem_bytes<T>(h);
   switch (h->cfg.integ_ns) {
     case 1: return configure_kernel<T, 1>(h, smem);
     case 2: return configure_kernel<T, 2>(h, smem);
@@ -264,7 +276,8 @@ int nmpc_create(const nmpc_config_t* cfg, int32_t batch, int32_t device, nmpc_ha
   h->ws_bytes = (size_t)h->nslots * h->L.total * esz;
   const size_t N = cfg->N, B = batch;
   CK(cudaMalloc(&h->ws, h->ws_bytes));
-  CK(cudaMalloc(&h->xtraj, B * (N + 1) * NX * sizeof(double)));
+  // +16 B: the 16-byte aligned range the TMA copies for the last problem may end 8 B past its row
+  CK(cudaMalloc(&h->xtraj, B * (N + 1) * NX * sizeof(double) + 16));
   CK(cudaMalloc(&h->utraj, B * N * NU * sizeof(double)));
   CK(cudaMalloc(&h->last_cmd, B * NU * sizeof(double)));
   CK(cudaMalloc(&h->valid, B));
@@ -280,7 +293,7 @@ int nmpc_create(const nmpc_config_t* cfg, int32_t batch, int32_t device, nmpc_ha
   CK(cudaMalloc(&h->s_status, B * sizeof(int)));
   CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   CK(cudaMemset(h->ws, 0, h->ws_bytes));
-  CK(cudaMemset(h->xtraj, 0, B * (N + 1) * NX * sizeof(double)));
+  CK(cudaMemset(h->xtraj, 0, B * (N + 1) * NX * sizeof(double) + 16));
   CK(cudaMemset(h->utraj, 0, B * N * NU * sizeof(double)));
   CK(cudaMemset(h->valid, 0, B));
   CK(cudaMemset(h->qp_iters, 0, B * sizeof(int)));
@@ -400,9 +413,12 @@ static int launch_solve(nmpc_handle* h, const double* x0, const double* yref, co
   A.qp_iters = h->qp_iters;
   A.sqp_iters = h->sqp_iters;
   A.ws = reinterpret_cast<T*>(h->ws);
-  const size_t smem = (size_t)WARPS * smem_elems_per_warp() * sizeof(T);
+  // bulk copies need 16-byte aligned sources: the caller's yref may not be (then direct loads)
+  A.stage = (h->stage_bytes > 0 && (reinterpret_cast<uintptr_t>(yref) & 15) == 0) ? 1 : 0;
+  const size_t smem = solve_smem_bytes<T>(h);
   CK(cudaMemsetAsync(h->counter, 0, sizeof(int), st));
-  nmpc_solve_kernel<T, NS><<<h->grid, WARPS * 32, smem, st>>>(A, h->L, h->counter);
+  nmpc_solve_kernel<T, NS>
+      <<<h->grid, WARPS * 32, smem, st>>>(A, h->L, h->counter);
   h->launches++;
   CK(cudaGetLastError());
   return NMPC_OK;

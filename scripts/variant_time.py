@@ -32,3 +32,27 @@ def run(name, B, sqp):
 run('cfg2', 4096, True)
 run('aggr', 65536, False)
 run('cfg2', 65536, False)
+
+
+def closed_loop(B=65536, steps=50):
+    """Warm-started RTI in closed loop with the device plant (configs[2] shape)."""
+    from rotors_mpc_controller_b200 import ClosedLoop, Plant
+    ctl = BatchedPositionNMPC(copy.deepcopy(params), batch=B)
+    cl = ClosedLoop(ctl, Plant(dt=ctl.dt, substeps=5))
+    rng = np.random.default_rng(1)
+    x = random_states(rng, B)
+    sp = x[:, 0:3] + np.concatenate([rng.uniform(-2, 2, (B, 2)), rng.uniform(-0.5, 0.5, (B, 1))], 1)
+    ms = []
+    for rep in range(3):
+        cl.reset(x)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); cl.run_setpoint(steps, sp); e1.record(); torch.cuda.synchronize()
+        ms.append(e0.elapsed_time(e1))
+    m = float(np.median(ms[1:]))
+    s = cl.summary(reduce=False)
+    print(f'{tag:16s} loop  B={B:6d} steps={steps} {m:8.3f} ms {B*steps/m*1e3:10.0f} solves/s  failed {s["failed_solves"]}', flush=True)
+    ctl.close()
+
+
+closed_loop()

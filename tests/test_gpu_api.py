@@ -234,3 +234,70 @@ def test_fp32_sqp_with_warm_start(params):
     rel = np.abs(res['f32'][0] - res['f64'][0]).max() / np.abs(res['f64'][0]).max()
     assert rel < 1e-3
     assert res['f32'][2] < 1.2 * res['f64'][2]        # no extra interior-point iterations
+
+
+def test_tma_staging_matches_direct_loads(params, O, monkeypatch):
+    """The solve kernel stages yref / the warm-start rows with TMA bulk copies when the horizon is
+    even and the caller's yref is 16-byte aligned, and reads them directly otherwise.  Same
+    problems through (a) the staged path, (b) a device yref that is only 8-byte aligned (falls
+    back to direct loads), (c) the NMPC_B200_NO_TMA handle: bit-identical results, cold and warm
+    (odd problem indices exercise the 8-byte offset of the staged warm-start rows)."""
+    import torch
+    B = 257
+    rng = np.random.default_rng(11)
+    ctl = _ctl(params, B)
+    x0, yref, yref_e = aggressive(rng, B, 20, ctl.hover_thrust)
+    dev = torch.device('cuda', 0)
+    X, Z = torch.as_tensor(x0, device=dev), torch.as_tensor(yref_e, device=dev)
+    Ya = torch.as_tensor(yref, device=dev)
+    assert Ya.data_ptr() % 16 == 0
+    raw = torch.empty(yref.size + 1, dtype=torch.float64, device=dev)
+    Ym = raw[1:].view(B, 20, 17)
+    Ym.copy_(Ya)
+    assert Ym.data_ptr() % 16 == 8 and Ym.is_contiguous()
+
+    def run(c, Y):
+        out = []
+        for _ in range(3):  # cold, then two warm-started solves
+            u0, st = c.solve(X, Y, Z)
+            out.append((u0.cpu().numpy().copy(), st.cpu().numpy().copy(),
+                        c.stats()['qp_iters'].copy(), c.trajectories()[0].copy()))
+        return out
+
+    staged = run(ctl, Ya)
+    ctl.invalidate()
+    direct = run(ctl, Ym)
+    ctl.close()
+    monkeypatch.setenv('NMPC_B200_NO_TMA', '1')
+    ctl2 = _ctl(params, B)
+    monkeypatch.delenv('NMPC_B200_NO_TMA')
+    knob = run(ctl2, Ya)
+    ctl2.close()
+    for a, b, c in zip(staged, direct, knob):
+        for i in range(4):
+            assert np.array_equal(a[i], b[i]) and np.array_equal(a[i], c[i])
+    ob = O.OracleBatch(O.config_from_params(params), B)
+    ur, sr, _, _ = ob.solve(x0, yref, yref_e)
+    assert np.array_equal(staged[0][1], sr)
+    assert np.max(np.abs(staged[0][0] - ur)) < TOL_U
+
+
+def test_odd_horizon_uses_direct_loads(params, O):
+    """Odd N: yref rows are not 16-byte multiples, staging is off; results still match the oracle."""
+    p = copy.deepcopy(params)
+    p['solver']['horizon_steps'] = 15
+    B = 64
+    ctl = _ctl(p, B)
+    rng = np.random.default_rng(12)
+    x0 = random_states(rng, B)
+    yref, yref_e = setpoint_refs(rng, x0, 15, ctl.hover_thrust)
+    u0, st = (a.copy() for a in ctl.solve(x0, yref, yref_e))   # the handle reuses its output arrays
+    u1, st1 = ctl.solve(x0, yref, yref_e)                      # warm-started second solve
+    ob = O.OracleBatch(O.config_from_params(p), B)
+    ur, sr, _, _ = ob.solve(x0, yref, yref_e)
+    assert np.array_equal(st, sr)
+    assert np.max(np.abs(u0 - ur)) < TOL_U
+    ur1, sr1, _, _ = ob.solve(x0, yref, yref_e)
+    assert np.array_equal(st1, sr1)
+    assert np.max(np.abs(u1 - ur1)) < TOL_U
+    ctl.close()
