@@ -117,7 +117,11 @@ int nmpc_reset_last_command(nmpc_handle_t *h);
  *   x0[batch,13] (quaternion already normalised, controller.py:406-411)
  *   yref[batch,N,17], yref_e[batch,13]                   (controller.py:433-445)
  *   u0[batch,4], status[batch] (int32), thrust[batch,4], speed[batch,4]; any output may be NULL.
- * Asynchronous on `stream` (a cudaStream_t, NULL = default stream). */
+ * Asynchronous on `stream` (a cudaStream_t, NULL = default stream).
+ * Any 8-byte aligned pointers work; with a 16-byte aligned `yref` (cudaMalloc / torch allocations
+ * are) and an even horizon the kernel stages the per-problem rows with TMA bulk copies, otherwise
+ * it reads them with plain loads (same results).  Environment: NMPC_B200_NO_TMA=1 at
+ * nmpc_create time forces the plain loads. */
 int nmpc_solve_device(nmpc_handle_t *h, const double *x0, const double *yref, const double *yref_e,
                       double *u0, int32_t *status, double *thrust, double *speed, void *stream);
 

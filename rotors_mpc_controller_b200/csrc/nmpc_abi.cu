@@ -35,10 +35,13 @@ constexpr int WARPS = NMPC_WARPS;  // warps (= problems in flight) per CTA
 constexpr int smem_elems_per_warp() { return smem_tile_elems(); }
 
 // ---------------------------------------------------------------- kernels
-template <typename T, int NS>
+// NF > 0: instantiation for a horizon known at compile time (see fixed_layout); NF = 0: any N.
+template <typename T, int NS, int NF>
 __global__ void __maxnreg__(sizeof(T) == 4 ? NMPC_MAXNREG_F32 : NMPC_MAXNREG)
-    nmpc_solve_kernel(const __grid_constant__ SolveArgs<T> A, const __grid_constant__ WsLayout L,
+    nmpc_solve_kernel(const __grid_constant__ SolveArgs<T> A, const __grid_constant__ WsLayout Lr,
                       int* __restrict__ work_counter) {
+  const WsLayout Lfix_ = NF > 0 ? make_layout(NF > 0 ? NF : 1) : WsLayout();
+  const WsLayout& L = NF > 0 ? Lfix_ : Lr;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   T* sm = reinterpret_cast<T*>(smem_raw) + warp * smem_elems_per_warp();
@@ -48,7 +51,7 @@ __global__ void __maxnreg__(sizeof(T) == 4 ? NMPC_MAXNREG_F32 : NMPC_MAXNREG)
   }
   const int slot = blockIdx.x * WARPS + warp;
   T* ws = A.ws + (size_t)slot * L.total;
-  init_position_columns(A.cfg.N, ws, L, lane);  // constant columns e_a of every A_k
+  init_position_columns(NF > 0 ? NF : A.cfg.N, ws, L, lane);  // constant columns e_a of every A_k
   __syncwarp();
   // dynamic work queue: iteration counts differ per problem, so problems are handed out one
   // at a time instead of in a fixed stride
@@ -57,7 +60,7 @@ __global__ void __maxnreg__(sizeof(T) == 4 ? NMPC_MAXNREG_F32 : NMPC_MAXNREG)
     if (lane == 0) prob = atomicAdd(work_counter, 1);
     prob = __shfl_sync(FULL, prob, 0);
     if (prob >= A.batch) break;
-    solve_one<T, NS>(A, L, ws, sm, prob, lane);
+    solve_one<T, NS, NF>(A, L, ws, sm, prob, lane);
   }
 }
 
@@ -169,6 +172,7 @@ DevCfg<T> make_devcfg(const nmpc_config_t& c) {
 struct nmpc_handle {
   nmpc_config_t cfg;
   int batch, device, sm_count, grid, nslots, launches;
+  int fixed_n;      // 1: the N = 20 instantiation of the solve kernel runs
   int stage_bytes;  // bytes of inputs the solve kernel stages by TMA per problem (0: direct loads)
   WsLayout L;
   size_t ws_bytes;
@@ -207,9 +211,16 @@ static int validate(const nmpc_config_t* c) {
   return NMPC_OK;
 }
 
-template <typename T, int NS>
+// The reference's default horizon (config/params.yaml: horizon_steps 20) with its default
+// integrator runs the fixed-horizon instantiation.
+constexpr int N_FIXED = 20;
+static bool use_fixed_horizon(const nmpc_handle* h) {
+  return h->cfg.N == N_FIXED && h->cfg.integ_ns == 2 && !getenv("NMPC_B200_GENERIC_N");
+}
+
+template <typename T, int NS, int NF>
 static int configure_kernel(nmpc_handle* h, size_t smem) {
-  auto kern = nmpc_solve_kernel<T, NS>;
+  auto kern = nmpc_solve_kernel<T, NS, NF>;
   CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int occ = 0;
   CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, WARPS * 32, smem));
@@ -233,13 +244,16 @@ static size_t solve_smem_bytes(const nmpc_handle* h) {
 
 template <typename T>
 static int configure_T(nmpc_handle* h) {
+  h->fixed_n = use_fixed_horizon(h) ? 1 : 0;
   h->stage_bytes = make_stage_layout(h->cfg.N, (int)sizeof(T)).total;
   if (getenv("NMPC_B200_NO_TMA")) h->stage_bytes = 0;  // A/B knob: direct loads of the inputs
   const size_t smem = solve_smem_bytes<T>(h);
   switch (h->cfg.integ_ns) {
-    case 1: return configure_kernel<T, 1>(h, smem);
-    case 2: return configure_kernel<T, 2>(h, smem);
-    default: return configure_kernel<T, 4>(h, smem);
+    case 1: return configure_kernel<T, 1, 0>(h, smem);
+    case 2:
+      return h->fixed_n ? configure_kernel<T, 2, N_FIXED>(h, smem)
+                        : configure_kernel<T, 2, 0>(h, smem);
+    default: return configure_kernel<T, 4, 0>(h, smem);
   }
 }
 
@@ -392,7 +406,7 @@ int nmpc_invalidate(nmpc_handle_t* h, const uint8_t* mask) {
 }
 
 extern "C++" {
-template <typename T, int NS>
+template <typename T, int NS, int NF>
 static int launch_solve(nmpc_handle* h, const double* x0, const double* yref, const double* yref_e,
                         double* u0, int32_t* status, double* thrust, double* speed,
                         cudaStream_t st) {
@@ -417,7 +431,7 @@ static int launch_solve(nmpc_handle* h, const double* x0, const double* yref, co
   A.stage = (h->stage_bytes > 0 && (reinterpret_cast<uintptr_t>(yref) & 15) == 0) ? 1 : 0;
   const size_t smem = solve_smem_bytes<T>(h);
   CK(cudaMemsetAsync(h->counter, 0, sizeof(int), st));
-  nmpc_solve_kernel<T, NS>
+  nmpc_solve_kernel<T, NS, NF>
       <<<h->grid, WARPS * 32, smem, st>>>(A, h->L, h->counter);
   h->launches++;
   CK(cudaGetLastError());
@@ -429,9 +443,12 @@ static int launch_solve_T(nmpc_handle* h, const double* x0, const double* yref,
                           const double* yref_e, double* u0, int32_t* status, double* thrust,
                           double* speed, cudaStream_t st) {
   switch (h->cfg.integ_ns) {
-    case 1: return launch_solve<T, 1>(h, x0, yref, yref_e, u0, status, thrust, speed, st);
-    case 2: return launch_solve<T, 2>(h, x0, yref, yref_e, u0, status, thrust, speed, st);
-    default: return launch_solve<T, 4>(h, x0, yref, yref_e, u0, status, thrust, speed, st);
+    case 1: return launch_solve<T, 1, 0>(h, x0, yref, yref_e, u0, status, thrust, speed, st);
+    case 2:
+      return h->fixed_n
+                 ? launch_solve<T, 2, N_FIXED>(h, x0, yref, yref_e, u0, status, thrust, speed, st)
+                 : launch_solve<T, 2, 0>(h, x0, yref, yref_e, u0, status, thrust, speed, st);
+    default: return launch_solve<T, 4, 0>(h, x0, yref, yref_e, u0, status, thrust, speed, st);
   }
 }
 }  // extern "C++"

@@ -86,6 +86,17 @@ __host__ __device__ inline WsLayout make_layout(int N) {
   return L;
 }
 
+// Horizon known at compile time (NF > 0: the kernel instantiation for the reference's default
+// N = 20): every workspace offset and loop bound folds into the instructions -- what acados gets
+// from generating code for a fixed horizon.  NF = 0: the layout and N are run-time values.
+// (NF = 0 must keep using the caller's layout object -- the kernel parameter in constant memory --
+// and not a copy: a copy is address-taken by the sweep calls and would live on the stack.)
+#define NMPC_FIXED(c_)                                                   \
+  const WsLayout Lfix_ = NF > 0 ? make_layout(NF > 0 ? NF : 1) : WsLayout(); \
+  const WsLayout& L = NF > 0 ? Lfix_ : Lr;                               \
+  const int N = NF > 0 ? NF : (c_).N;                                    \
+  (void)N;
+
 // Per-warp shared-memory tile (elements of T).
 constexpr int SP_LD = 14;  // padded leading dimension of P and K rows (16-byte aligned rows)
 struct SmemLayout {
@@ -216,13 +227,14 @@ __device__ __forceinline__ void init_position_columns(int N, T* __restrict__ ws,
   }
 }
 
-template <typename T, int NS>
+template <typename T, int NS, int NF>
 __device__ __forceinline__ void linearize(const DevCfg<T>& c, T* __restrict__ ws,
-                                          const WsLayout& L, T* __restrict__ sm, int lane) {
+                                          const WsLayout& Lr, T* __restrict__ sm, int lane) {
+  NMPC_FIXED(c)
   // The iterate is read stage by stage below (17 broadcast loads per pass, each pass would wait
   // for L2): when it fits the (idle) stage buffers it is copied to shared memory once, with all
   // loads in flight together.
-  const int nxv = (c.N + 1) * NX, nuv = c.N * NU;
+  const int nxv = (N + 1) * NX, nuv = N * NU;
   const bool staged = nxv + nuv <= SmemLayout::K - SmemLayout::M;
   const T* xb = ws + L.xb;
   const T* ub = ws + L.ub;
@@ -240,9 +252,9 @@ __device__ __forceinline__ void linearize(const DevCfg<T>& c, T* __restrict__ ws
   const bool ccol = cl < NZ - 3;              // 14 integrated columns per stage
   const int sx = cl - 1;                      // state seeded by lanes 4..13: v, q, w = 3..12
   const int zc = cl < NU ? cl : cl + 3;       // column of M_k = [B | A]
-  for (int k0 = 0; k0 < c.N; k0 += 2) {
-    const bool live = k0 + h < c.N;           // odd horizons: the upper half idles on the last pass
-    const int k = live ? k0 + h : c.N - 1;
+  for (int k0 = 0; k0 < N; k0 += 2) {
+    const bool live = k0 + h < N;           // odd horizons: the upper half idles on the last pass
+    const int k = live ? k0 + h : N - 1;
     T x[NX], u[NU], s[NX], su[NU];
 #pragma unroll
     for (int i = 0; i < NX; i++) {
@@ -271,11 +283,11 @@ __device__ __forceinline__ void linearize(const DevCfg<T>& c, T* __restrict__ ws
 }
 
 // LINEAR_LS gradients (controller.py:223-245, stage cost scaled by dt) and the delta-form box.
-template <typename T>
+template <typename T, int NF>
 __device__ __noinline__ void gradients(const DevCfg<T>& c, T* __restrict__ ws,
-                                          const WsLayout& L, const double* __restrict__ yref,
-                                          const double* __restrict__ yref_e, int lane) {
-  const int N = c.N;
+                                       const WsLayout& Lr, const double* __restrict__ yref,
+                                       const double* __restrict__ yref_e, int lane) {
+  NMPC_FIXED(c)
   const T* xb = ws + L.xb;
   const T* ub = ws + L.ub;
   _Pragma("unroll 3") for (int idx = lane; idx < N * NX; idx += 32) {
@@ -311,12 +323,12 @@ namespace nmpc {
 //           and phase 0 is skipped (start at dz = 0, residuals b and q scaled by rho as well).
 // Returns the QP status; *iters = number of Riccati factorisations; *ipm_conv = the interior-point
 // loop ran and met its tolerance (its iterate is a valid warm start for the next QP).
-template <typename T>
+template <typename T, int NF>
 __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
-                                         const WsLayout& L, T* __restrict__ sm, int lane,
+                                         const WsLayout& Lr, T* __restrict__ sm, int lane,
                                          T warm_eps, bool* ipm_conv, int* iters) {
   *ipm_conv = false;
-  const int N = c.N;
+  NMPC_FIXED(c)
   const int nb = N * NU;
   const int nxv = (N + 1) * NX;
   const T thr0 = T(0.1), mu0 = T(0.1);
@@ -354,13 +366,13 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
   __syncwarp();
   if (!skip0) {
     res0 = T(0);  // b and q are met exactly by the phase-0 point
-    const bool ok0 = factor_sweep(c, ws, L, sm, lane, T(1));
+    const bool ok0 = factor_sweep<T, NF>(c, ws, L, sm, lane, T(1));
     it = 1;
     if (!ok0) {
       *iters = it;
       return ST_QPFAIL;
     }
-    forward_sweep<T>(c, ws, L, sm, lane, T(1), false, true, false, L.kff, L.dx, L.du);
+    forward_sweep<T, NF>(c, ws, L, sm, lane, T(1), false, true, false, L.kff, L.dx, L.du);
   }
   // box check + interior-point start
   bool feas = !skip0;
@@ -449,14 +461,14 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
     }
     __syncwarp();
     const T rq = skip0 ? rho : T(0);
-    const bool ok = factor_sweep(c, ws, L, sm, lane, rq);
+    const bool ok = factor_sweep<T, NF>(c, ws, L, sm, lane, rq);
     if (!ok) {
       // FP32 precision floor: once the complementarity is below 1e-6 a lost pivot means the
       // barrier Hessian can no longer be resolved in single precision -> keep the iterate
       status = (sizeof(T) == 4 && mu <= T(1e-6)) ? ST_SUCCESS : ST_QPFAIL;
       break;
     }
-    forward_sweep<T>(c, ws, L, sm, lane, rq, false, false, false, L.kff, L.dx, L.ua);   // wx = false: no state output
+    forward_sweep<T, NF>(c, ws, L, sm, lane, rq, false, false, false, L.kff, L.dx, L.ua);   // wx = false: no state output
     // affine step length (division-free ratio test: the running minimum is kept as a fraction
     // an/ad and candidates are compared by cross-multiplication)
     T an = T(1), ad = T(1);
@@ -509,8 +521,8 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
     })
     __syncwarp();
     // corrector increment (vector-only re-solve), accumulated onto the predictor direction
-    delta_backward(c, ws, L, sm, lane);
-    forward_sweep<T>(c, ws, L, sm, lane, T(0), true, false, false, L.kffd, L.dx, L.ua);
+    delta_backward<T, NF>(c, ws, L, sm, lane);
+    forward_sweep<T, NF>(c, ws, L, sm, lane, T(0), true, false, false, L.kffd, L.dx, L.ua);
     T bn = T(2), bd = T(1);  // ratios >= 2 cannot bind: alpha = min(1, tau * ratio), tau >= 0.995
     bool fin = true;         // NaN anywhere must surface: comparisons drop NaNs, so test explicitly
     NMPC_ROWS({
@@ -586,7 +598,7 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
   // The state direction is only needed once: roll the linearised dynamics out for the final
   // input direction, dx_{k+1} = A_k dx_k + B_k du_k + b_k (instead of updating dx every iteration).
   __syncwarp();
-  forward_sweep<T>(c, ws, L, sm, lane, T(1), false, true, true, L.kff, L.dx, L.du);
+  forward_sweep<T, NF>(c, ws, L, sm, lane, T(1), false, true, true, L.kff, L.dx, L.du);
   *iters = it;
   *ipm_conv = (status == ST_SUCCESS);
   return status;
@@ -624,12 +636,12 @@ __device__ __forceinline__ T clip_(T v, T lo, T hi) {
 // tile (see StageLayout) and are consumed from shared memory before this function returns -- the
 // tile is free again for linearize and the sweeps; without it they are read from HBM directly.
 // (Inlined into solve_one, with gradients() as a call: measured best of the four combinations.)
-template <typename T>
-__device__ __forceinline__ void load_inputs(const SolveArgs<T>& A, const WsLayout& L,
-                                         T* __restrict__ ws, T* __restrict__ sm, int prob,
-                                         int lane) {
+template <typename T, int NF>
+__device__ __forceinline__ void load_inputs(const SolveArgs<T>& A, const WsLayout& Lr,
+                                            T* __restrict__ ws, T* __restrict__ sm, int prob,
+                                            int lane) {
   const DevCfg<T>& c = A.cfg;
-  const int N = c.N;
+  NMPC_FIXED(c)
   const int nxv = (N + 1) * NX, nuv = N * NU;
   const double* x0 = A.x0 + (size_t)prob * NX;
   const double* yref = A.yref + (size_t)prob * N * NZ;
@@ -673,24 +685,24 @@ __device__ __forceinline__ void load_inputs(const SolveArgs<T>& A, const WsLayou
   }
   _Pragma("unroll 1") for (int i = lane; i < nuv; i += 32) ws[L.ub + i] = warm ? (T)u_in[i] : T(0);
   __syncwarp();
-  gradients(c, ws, L, yref, yref_e, lane);
+  gradients<T, NF>(c, ws, L, yref, yref_e, lane);
   __syncwarp();  // the staged references are consumed: the tile goes back to the sweeps
 }
 
 // One PositionNMPC.solve() (controller.py:385-463) + the node's command map
 // (nodes/mpc_controller_node:124-131,152-164) for problem `prob`, executed by one warp.
-template <typename T, int NS>
-__device__ __forceinline__ void solve_one(const SolveArgs<T>& A, const WsLayout& L, T* ws, T* sm,
+template <typename T, int NS, int NF>
+__device__ __forceinline__ void solve_one(const SolveArgs<T>& A, const WsLayout& Lr, T* ws, T* sm,
                                           int prob, int lane) {
   const DevCfg<T>& c = A.cfg;
-  const int N = c.N;
+  NMPC_FIXED(c)
   const int nxv = (N + 1) * NX, nuv = N * NU;
   const double* yref = A.yref + (size_t)prob * N * NZ;
   const double* yref_e = A.yref_e + (size_t)prob * NX;
   double* xtraj = A.xtraj + (size_t)prob * nxv;
   double* utraj = A.utraj + (size_t)prob * nuv;
   // inputs -> workspace (TMA-staged when possible) + the gradients of the first SQP iteration
-  load_inputs(A, L, ws, sm, prob, lane);
+  load_inputs<T, NF>(A, L, ws, sm, prob, lane);
 
   int status = ST_SUCCESS;
   int tot_qp = 0, nsqp = 0;
@@ -701,14 +713,14 @@ __device__ __forceinline__ void solve_one(const SolveArgs<T>& A, const WsLayout&
   const T eps_min = sizeof(T) == 4 ? T(1e-4) : T(NMPC_WARM_EPS_MIN);
   const int max_sqp = c.max_sqp_iter < 1 ? 1 : c.max_sqp_iter;
   while (nsqp < max_sqp) {
-    linearize<T, NS>(c, ws, L, sm, lane);
-    if (nsqp > 0) gradients(c, ws, L, yref, yref_e, lane);  // first iteration: done by load_inputs
+    linearize<T, NS, NF>(c, ws, L, sm, lane);
+    if (nsqp > 0) gradients<T, NF>(c, ws, L, yref, yref_e, lane);  // first iteration: done by load_inputs
     __syncwarp();
     int qi = 0;
     T weps = T(0);
     if (c.ipm_warm && have_ipm && prev_step <= T(NMPC_WARM_STEP_MAX))
       weps = fmin(fmax(T(NMPC_WARM_KAPPA) * prev_step, eps_min), T(NMPC_WARM_EPS_MAX));
-    const int qs = ipm_solve(c, ws, L, sm, lane, weps, &have_ipm, &qi);
+    const int qs = ipm_solve<T, NF>(c, ws, L, sm, lane, weps, &have_ipm, &qi);
     tot_qp += qi;
     nsqp++;
     // acados SQP_RTI tolerates a QP that only hit its iteration cap
