@@ -301,3 +301,35 @@ def test_odd_horizon_uses_direct_loads(params, O):
     assert np.array_equal(st1, sr1)
     assert np.max(np.abs(u1 - ur1)) < TOL_U
     ctl.close()
+
+
+def test_fixed_horizon_kernel_matches_generic(params, monkeypatch):
+    """N = 20 with the midpoint integrator runs the kernel instantiation with the horizon folded
+    in at compile time; NMPC_B200_GENERIC_N=1 (read at nmpc_create) forces the run-time-N
+    instantiation that every other horizon uses.  Same arithmetic in the same order: bit-identical
+    results, cold and warm, RTI and SQP."""
+    B = 300
+    rng = np.random.default_rng(21)
+    p = copy.deepcopy(params)
+    p['solver']['max_sqp_iter'] = 50
+    p['solver']['sqp_tol'] = 1e-8
+    outs = []
+    for generic in (False, True):
+        if generic:
+            monkeypatch.setenv('NMPC_B200_GENERIC_N', '1')
+        res = []
+        for prm in (params, p):
+            ctl = _ctl(prm, B)
+            r = np.random.default_rng(21)
+            x0, yref, yref_e = aggressive(r, B, 20, ctl.hover_thrust)
+            for _ in range(2):
+                u0, st = ctl.solve(x0, yref, yref_e)
+                res.append((u0.copy(), st.copy(), ctl.stats()['qp_iters'].copy(),
+                            ctl.trajectories()[0].copy()))
+            ctl.close()
+        outs.append(res)
+        if generic:
+            monkeypatch.delenv('NMPC_B200_GENERIC_N')
+    for a, b in zip(*outs):
+        for i in range(4):
+            assert np.array_equal(a[i], b[i])
