@@ -109,7 +109,8 @@ struct SmemLayout {
   static constexpr int xA = wv + 14;             // 13 (+1) forward-sweep state, ping
   static constexpr int xB = xA + 14;             // pong
   static constexpr int bar = xB + 14;            // mbarrier of the input staging + its parity
-  static constexpr int total = bar + 4;          // 1004 elements
+  static constexpr int G = bar + 4;              // 16 x 4 exchange tile of factor_sweep + 4 (g_u)
+  static constexpr int total = G + 68;           // 1072 elements
 };
 
 // ------------------------------------------------------------------ TMA input staging
