@@ -415,7 +415,10 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
   // Element-wise passes over the nb = 4N box rows.  NSL rows per lane and trip: all loads of a
   // trip are issued before any arithmetic or store.  NSL = 1 keeps the code small (the instruction
   // cache, not the L2 latency of these short loops, is what the passes compete for).
-  constexpr int NSL = 1;
+#ifndef NMPC_NSL
+#define NMPC_NSL 1
+#endif
+  constexpr int NSL = NMPC_NSL;
 #define NMPC_ROWS(...)                                                \
   _Pragma("unroll 1") for (int base_ = 0; base_ < nb; base_ += 32 * NSL) { \
     int ix[NSL];                                                      \
