@@ -55,7 +55,8 @@ typedef struct nmpc_config {
   int32_t integ_ns;        /* sim_method_num_stages: 1 Euler, 2 midpoint (ref), 4 RK4 */
   int32_t integ_steps;     /* sim_method_num_steps (ref: 2) */
   int32_t cost_scale_dt;   /* stage cost scaled by dt (acados default: 1) */
-  int32_t lm_scaled_by_dt; /* LM term scaled by dt (default 0) */
+  int32_t lm_scaled_by_dt; /* LM term of stages 0..N-1 scaled by dt like the stage cost (acados: Ts[i] *
+                              levenberg_marquardt; terminal stage unscaled).  Default 1; 0 = unscaled */
   int32_t max_sqp_iter;    /* 1 = SQP_RTI (reference); >1 = SQP until step <= sqp_tol */
   int32_t nan_status;      /* status reported when NaNs appear in the iterate (4 or 1) */
   int32_t precision;       /* NMPC_PRECISION_F64 | NMPC_PRECISION_F32 */
@@ -106,9 +107,14 @@ int nmpc_reconfigure(nmpc_handle_t *h, const nmpc_config_t *cfg);
 /* Override the input box (default: controller.py:105-110). */
 int nmpc_set_bounds(nmpc_handle_t *h, const double lbu[4], const double ubu[4]);
 
-/* _prev_solution_valid = False for problems with mask[i] != 0 (all when mask == NULL);
- * host pointer. */
+/* _prev_solution_valid = False (controller.py:167, :449) for problems with mask[i] != 0 (all when
+ * mask == NULL).  `mask` is a HOST pointer; the call returns when the flags are cleared, so a
+ * solve enqueued afterwards on any stream sees them.  It waits for this handle's last kernel only
+ * (stream-scoped: other handles and streams of the process keep running). */
 int nmpc_invalidate(nmpc_handle_t *h, const uint8_t *mask);
+/* Same with a DEVICE mask (or NULL), asynchronous on `stream` (a cudaStream_t): one tiny kernel,
+ * no host synchronisation -- for closed-loop runs that reset problems between control steps. */
+int nmpc_invalidate_device(nmpc_handle_t *h, const uint8_t *mask, void *stream);
 /* Reset the last-valid command to hover thrust (all problems). */
 int nmpc_reset_last_command(nmpc_handle_t *h);
 
@@ -131,7 +137,9 @@ int nmpc_solve_host(nmpc_handle_t *h, const double *x0, const double *yref, cons
 
 /* Copy out the warm-start store / statistics (dst_is_device: 0 host, 1 device).
  * xtraj[batch,N+1,13], utraj[batch,N,4], valid[batch] (uint8), qp_iters[batch] (int32, number of
- * Riccati factorisations), sqp_iters[batch] (int32).  NULL pointers are skipped.  Synchronous. */
+ * Riccati factorisations), sqp_iters[batch] (int32).  NULL pointers are skipped.  Synchronous for
+ * the caller, stream-scoped on the device: the copies queue behind this handle's last kernel on
+ * the handle's own stream (no cudaDeviceSynchronize; other streams keep running). */
 int nmpc_get_trajectories(nmpc_handle_t *h, double *xtraj, double *utraj, uint8_t *valid,
                           int32_t dst_is_device);
 int nmpc_get_stats(nmpc_handle_t *h, int32_t *qp_iters, int32_t *sqp_iters, int32_t dst_is_device);

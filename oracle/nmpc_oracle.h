@@ -57,7 +57,7 @@ typedef struct {
   int integ_ns;       /* sim_method_num_stages (1,2,4)       controller.py:187 */
   int integ_steps;    /* sim_method_num_steps                controller.py:188 */
   int cost_scale_dt;  /* acados cost scaling by time step (default 1) */
-  int lm_scaled_by_dt;/* LM term scaled by dt (default 0) */
+  int lm_scaled_by_dt;/* LM term of stages 0..N-1 scaled by dt (default 1; terminal unscaled) */
   int max_sqp_iter;   /* 1 = SQP_RTI (reference), >1 = SQP extension */
   double sqp_tol;     /* inf-norm step tolerance for max_sqp_iter>1 */
   double ipm_tol;     /* complementarity / residual tolerance of the QP IPM */

@@ -121,7 +121,7 @@ def config_from_params(params: Dict[str, Dict[str, object]], **flags) -> OrcConf
     c.integ_ns = int(flags.get('integ_ns', 2))
     c.integ_steps = int(flags.get('integ_steps', 2))
     c.cost_scale_dt = int(flags.get('cost_scale_dt', 1))
-    c.lm_scaled_by_dt = int(flags.get('lm_scaled_by_dt', 0))
+    c.lm_scaled_by_dt = int(flags.get('lm_scaled_by_dt', 1))
     c.max_sqp_iter = int(flags.get('max_sqp_iter', 1))
     c.sqp_tol = float(flags.get('sqp_tol', 1e-8))
     c.ipm_tol = float(flags.get('ipm_tol', 1e-14))

@@ -68,6 +68,7 @@ SYMBOLS = {
     'nmpc_reconfigure': (C.c_int, [_vp, C.POINTER(NmpcConfig)]),
     'nmpc_set_bounds': (C.c_int, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     'nmpc_invalidate': (C.c_int, [_vp, _bp]),
+    'nmpc_invalidate_device': (C.c_int, [_vp, _bp, _vp]),
     'nmpc_reset_last_command': (C.c_int, [_vp]),
     'nmpc_solve_device': (C.c_int, [_vp, _dp, _dp, _dp, _dp, _ip, _dp, _dp, _vp]),
     'nmpc_solve_host': (C.c_int, [_vp, _dp, _dp, _dp, _dp, _ip, _dp, _dp]),

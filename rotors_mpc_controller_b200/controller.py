@@ -130,7 +130,7 @@ def abi_config(cp: ControllerParams, solver_cfg: Dict[str, object]) -> _abi.Nmpc
     c.integ_ns = _INTEGRATORS[integ]                       # ERK, num_stages=2 (:183,:187)
     c.integ_steps = int(solver_cfg.get('integrator_steps', 2))  # num_steps=2 (:188)
     c.cost_scale_dt = int(bool(solver_cfg.get('cost_scale_dt', True)))
-    c.lm_scaled_by_dt = int(bool(solver_cfg.get('lm_scaled_by_dt', False)))
+    c.lm_scaled_by_dt = int(bool(solver_cfg.get('lm_scaled_by_dt', True)))
     c.max_sqp_iter = int(solver_cfg.get('max_sqp_iter', 1))     # SQP_RTI (nlp_solver_type unset)
     c.nan_status = int(solver_cfg.get('nan_status', 4))
     c.ipm_warm_start = int(bool(solver_cfg.get('ipm_warm_start', True)))
@@ -281,7 +281,19 @@ class BatchedPositionNMPC:
 
     def invalidate(self, mask=None) -> None:
         """Drop the warm start (all problems, or those with mask != 0)."""
+        if mask is not None and hasattr(mask, 'data_ptr'):   # device mask: one async kernel
+            import torch
+            if (not mask.is_cuda or mask.dtype != torch.uint8 or not mask.is_contiguous()
+                    or mask.numel() != self.batch or mask.device.index != self.device):
+                raise ValueError('expected a contiguous CUDA uint8 mask of length batch on the '
+                                 "handle's device")
+            stream = torch.cuda.current_stream(mask.device).cuda_stream
+            _abi.check(_abi.lib().nmpc_invalidate_device(self._h.ptr, mask.data_ptr(), stream),
+                       'nmpc_invalidate_device')
+            return
         m = None if mask is None else np.ascontiguousarray(mask, dtype=np.uint8)
+        if m is not None and m.shape != (self.batch,):
+            raise ValueError('mask must have one entry per problem')
         _abi.check(_abi.lib().nmpc_invalidate(self._h.ptr, _abi.ptr(m)), 'nmpc_invalidate')
 
     def reset_last_command(self) -> None:
@@ -297,6 +309,9 @@ class BatchedPositionNMPC:
                 if (not t.is_cuda or t.dtype != torch.float64 or not t.is_contiguous()
                         or tuple(t.shape) != shape):
                     raise ValueError(f'expected contiguous CUDA float64 tensor of shape {shape}')
+                if t.device.index != self.device:
+                    raise ValueError(f'tensor on {t.device}, but this solver was built for '
+                                     f'cuda:{self.device}')
             if self._out is None or not hasattr(self._out[0], 'data_ptr'):
                 dev = x0.device
                 self._out = (torch.empty((B, 4), dtype=torch.float64, device=dev),

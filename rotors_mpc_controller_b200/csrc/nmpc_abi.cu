@@ -98,6 +98,13 @@ __global__ void fill_last_cmd_kernel(double* last, int n, double hover) {
   if (i < n) last[i] = hover;
 }
 
+// _prev_solution_valid = False (controller.py:167, :449) for the problems with mask[i] != 0
+// (all problems when mask is null).
+__global__ void invalidate_kernel(uint8_t* valid, const uint8_t* __restrict__ mask, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && (!mask || mask[i])) valid[i] = 0;
+}
+
 // DFMA throughput micro-benchmark: 8 independent FMA chains per thread (the FP64 roofline
 // denominator; MEASURED_PEAKS.json carries no FP64 figure).
 __global__ void __launch_bounds__(256) fp64_peak_kernel(double* out, int iters, double a, double b) {
@@ -183,8 +190,23 @@ struct nmpc_handle {
   // staging for nmpc_solve_host
   double *s_x0, *s_yref, *s_yref_e, *s_u0, *s_thrust, *s_speed;
   int* s_status;
-  cudaStream_t stream;
+  uint8_t* s_mask;       // staging of a host mask (nmpc_invalidate)
+  cudaStream_t stream;   // the handle's own stream (host-buffer calls, copies of the stores)
+  cudaEvent_t ev_last;   // recorded behind the last kernel this handle enqueued on a caller stream
+  // device-side constants, rebuilt only when the configuration changes
+  DevCfg<double> dc64;
+  DevCfg<float> dc32;
 };
+
+// The handle's stores (valid, warm start, statistics, last command) are written by kernels the
+// caller enqueues on streams of his choice.  Calls that touch the stores from the host side order
+// themselves behind the last such kernel through ev_last and run on the handle's own stream, so
+// they never synchronise the device (other handles / streams of the process keep running).
+static void mark_enqueued(nmpc_handle* h, cudaStream_t st) { cudaEventRecord(h->ev_last, st); }
+static cudaError_t order_behind_last(nmpc_handle* h) {
+  return cudaStreamWaitEvent(h->stream, h->ev_last, 0);
+}
+static void refresh_devcfg(nmpc_handle* h);
 
 #define CK(call)                                                                         \
   do {                                                                                   \
@@ -210,6 +232,17 @@ static int validate(const nmpc_config_t* c) {
     if (!(c->lbu[i] < c->ubu[i])) return NMPC_E_INVALID;
   return NMPC_OK;
 }
+
+static void refresh_devcfg(nmpc_handle* h) {
+  h->dc64 = make_devcfg<double>(h->cfg);
+  h->dc32 = make_devcfg<float>(h->cfg);
+}
+template <typename T>
+static const DevCfg<T>& devcfg_of(const nmpc_handle* h);
+template <>
+const DevCfg<double>& devcfg_of<double>(const nmpc_handle* h) { return h->dc64; }
+template <>
+const DevCfg<float>& devcfg_of<float>(const nmpc_handle* h) { return h->dc32; }
 
 // The reference's default horizon (config/params.yaml: horizon_steps 20) with its default
 // integrator runs the fixed-horizon instantiation.
@@ -259,36 +292,23 @@ static int configure_T(nmpc_handle* h) {
 
 extern "C" {
 
-int nmpc_create(const nmpc_config_t* cfg, int32_t batch, int32_t device, nmpc_handle_t** out) {
-  if (!out) return NMPC_E_INVALID;
-  *out = nullptr;
-  int rc = validate(cfg);
-  if (rc != NMPC_OK || batch < 1) return NMPC_E_INVALID;
-  int ndev = 0;
-  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) {
-    snprintf(g_err, sizeof(g_err), "no CUDA device (libnmpc_b200 has no CPU fallback)");
-    return NMPC_E_NODEVICE;
-  }
-  if (device < 0 || device >= ndev) return NMPC_E_INVALID;
-  CK(cudaSetDevice(device));
-  nmpc_handle* h = new (std::nothrow) nmpc_handle();
-  if (!h) return NMPC_E_NOMEM;
+static int create_impl(nmpc_handle* h, const nmpc_config_t* cfg, int batch, int device) {
   memset(h, 0, sizeof(*h));
   h->cfg = *cfg;
   h->batch = batch;
   h->device = device;
+  refresh_devcfg(h);
   cudaDeviceProp prop;
   CK(cudaGetDeviceProperties(&prop, device));
   h->sm_count = prop.multiProcessorCount;
   h->L = make_layout(cfg->N);
-  rc = (cfg->precision == NMPC_PRECISION_F64) ? configure_T<double>(h) : configure_T<float>(h);
-  if (rc != NMPC_OK) {
-    delete h;
-    return rc;
-  }
+  int rc = (cfg->precision == NMPC_PRECISION_F64) ? configure_T<double>(h) : configure_T<float>(h);
+  if (rc != NMPC_OK) return rc;
   const size_t esz = (cfg->precision == NMPC_PRECISION_F64) ? 8 : 4;
   h->ws_bytes = (size_t)h->nslots * h->L.total * esz;
   const size_t N = cfg->N, B = batch;
+  CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+  CK(cudaEventCreateWithFlags(&h->ev_last, cudaEventDisableTiming));
   CK(cudaMalloc(&h->ws, h->ws_bytes));
   // +16 B: the 16-byte aligned range the TMA copies for the last problem may end 8 B past its row
   CK(cudaMalloc(&h->xtraj, B * (N + 1) * NX * sizeof(double) + 16));
@@ -305,20 +325,48 @@ int nmpc_create(const nmpc_config_t* cfg, int32_t batch, int32_t device, nmpc_ha
   CK(cudaMalloc(&h->s_thrust, B * NU * sizeof(double)));
   CK(cudaMalloc(&h->s_speed, B * NU * sizeof(double)));
   CK(cudaMalloc(&h->s_status, B * sizeof(int)));
-  CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
-  CK(cudaMemset(h->ws, 0, h->ws_bytes));
-  CK(cudaMemset(h->xtraj, 0, B * (N + 1) * NX * sizeof(double) + 16));
-  CK(cudaMemset(h->utraj, 0, B * N * NU * sizeof(double)));
-  CK(cudaMemset(h->valid, 0, B));
-  CK(cudaMemset(h->qp_iters, 0, B * sizeof(int)));
-  CK(cudaMemset(h->sqp_iters, 0, B * sizeof(int)));
-  *out = h;
+  CK(cudaMalloc(&h->s_mask, B));
+  cudaStream_t st = h->stream;
+  CK(cudaMemsetAsync(h->ws, 0, h->ws_bytes, st));
+  CK(cudaMemsetAsync(h->xtraj, 0, B * (N + 1) * NX * sizeof(double) + 16, st));
+  CK(cudaMemsetAsync(h->utraj, 0, B * N * NU * sizeof(double), st));
+  CK(cudaMemsetAsync(h->valid, 0, B, st));
+  CK(cudaMemsetAsync(h->qp_iters, 0, B * sizeof(int), st));
+  CK(cudaMemsetAsync(h->sqp_iters, 0, B * sizeof(int), st));
+  CK(cudaEventRecord(h->ev_last, st));
   return nmpc_reset_last_command(h);
+}
+
+int nmpc_create(const nmpc_config_t* cfg, int32_t batch, int32_t device, nmpc_handle_t** out) {
+  if (!out) return NMPC_E_INVALID;
+  *out = nullptr;
+  int rc = validate(cfg);
+  if (rc != NMPC_OK || batch < 1) return NMPC_E_INVALID;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) {
+    snprintf(g_err, sizeof(g_err), "no CUDA device (libnmpc_b200 has no CPU fallback)");
+    return NMPC_E_NODEVICE;
+  }
+  if (device < 0 || device >= ndev) return NMPC_E_INVALID;
+  CK(cudaSetDevice(device));
+  nmpc_handle* h = new (std::nothrow) nmpc_handle();
+  if (!h) return NMPC_E_NOMEM;
+  rc = create_impl(h, cfg, batch, device);
+  if (rc != NMPC_OK) {  // nothing of a half-built handle survives (nmpc_destroy tolerates nulls)
+    nmpc_destroy(h);
+    return rc;
+  }
+  *out = h;
+  return NMPC_OK;
 }
 
 int nmpc_destroy(nmpc_handle_t* h) {
   if (!h) return NMPC_OK;
   cudaSetDevice(h->device);
+  if (h->stream) {
+    if (h->ev_last) cudaStreamWaitEvent(h->stream, h->ev_last, 0);
+    cudaStreamSynchronize(h->stream);  // the last kernel that uses the buffers has finished
+  }
   cudaFree(h->ws);
   cudaFree(h->xtraj);
   cudaFree(h->utraj);
@@ -334,6 +382,8 @@ int nmpc_destroy(nmpc_handle_t* h) {
   cudaFree(h->s_thrust);
   cudaFree(h->s_speed);
   cudaFree(h->s_status);
+  cudaFree(h->s_mask);
+  if (h->ev_last) cudaEventDestroy(h->ev_last);
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
   return NMPC_OK;
@@ -344,10 +394,22 @@ int nmpc_reset_last_command(nmpc_handle_t* h) {
   CK(cudaSetDevice(h->device));
   const int n = h->batch * NU;
   const double hover = h->cfg.mass * h->cfg.gravity / 4.0;  // mpc_controller_node:64
-  fill_last_cmd_kernel<<<(n + 255) / 256, 256>>>(h->last_cmd, n, hover);
+  CK(order_behind_last(h));
+  fill_last_cmd_kernel<<<(n + 255) / 256, 256, 0, h->stream>>>(h->last_cmd, n, hover);
   h->launches++;
   CK(cudaGetLastError());
-  CK(cudaDeviceSynchronize());
+  CK(cudaStreamSynchronize(h->stream));
+  return NMPC_OK;
+}
+
+int nmpc_invalidate_device(nmpc_handle_t* h, const uint8_t* mask, void* stream) {
+  if (!h) return NMPC_E_INVALID;
+  CK(cudaSetDevice(h->device));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  invalidate_kernel<<<(h->batch + 255) / 256, 256, 0, st>>>(h->valid, mask, h->batch);
+  h->launches++;
+  CK(cudaGetLastError());
+  mark_enqueued(h, st);
   return NMPC_OK;
 }
 
@@ -357,9 +419,9 @@ int nmpc_reconfigure(nmpc_handle_t* h, const nmpc_config_t* cfg) {
   if (rc != NMPC_OK) return rc;
   if (cfg->N != h->cfg.N || cfg->precision != h->cfg.precision) return NMPC_E_INVALID;
   CK(cudaSetDevice(h->device));
-  CK(cudaDeviceSynchronize());
   const int old_ns = h->cfg.integ_ns;
   h->cfg = *cfg;
+  refresh_devcfg(h);
   if (cfg->integ_ns != old_ns) {
     const int slots = h->nslots;
     rc = (cfg->precision == NMPC_PRECISION_F64) ? configure_T<double>(h) : configure_T<float>(h);
@@ -369,8 +431,7 @@ int nmpc_reconfigure(nmpc_handle_t* h, const nmpc_config_t* cfg) {
       h->grid = slots / WARPS;
     }
   }
-  CK(cudaMemset(h->valid, 0, h->batch));  // controller.py:167
-  return NMPC_OK;
+  return nmpc_invalidate(h, nullptr);  // controller.py:167
 }
 
 int nmpc_set_bounds(nmpc_handle_t* h, const double lbu[4], const double ubu[4]) {
@@ -381,27 +442,25 @@ int nmpc_set_bounds(nmpc_handle_t* h, const double lbu[4], const double ubu[4]) 
     h->cfg.lbu[i] = lbu[i];
     h->cfg.ubu[i] = ubu[i];
   }
+  refresh_devcfg(h);
   return NMPC_OK;
 }
 
 int nmpc_invalidate(nmpc_handle_t* h, const uint8_t* mask) {
   if (!h) return NMPC_E_INVALID;
   CK(cudaSetDevice(h->device));
-  CK(cudaDeviceSynchronize());
-  if (!mask) {
-    CK(cudaMemset(h->valid, 0, h->batch));
-    return NMPC_OK;
+  // behind the last solve of this handle, on the handle's own stream; the host waits for that
+  // stream only, so a solve enqueued afterwards on ANY stream sees the cleared flags
+  CK(order_behind_last(h));
+  const uint8_t* dmask = nullptr;
+  if (mask) {
+    CK(cudaMemcpyAsync(h->s_mask, mask, h->batch, cudaMemcpyHostToDevice, h->stream));
+    dmask = h->s_mask;
   }
-  uint8_t* tmp = new (std::nothrow) uint8_t[h->batch];
-  if (!tmp) return NMPC_E_NOMEM;
-  cudaError_t e = cudaMemcpy(tmp, h->valid, h->batch, cudaMemcpyDeviceToHost);
-  if (e == cudaSuccess) {
-    for (int i = 0; i < h->batch; i++)
-      if (mask[i]) tmp[i] = 0;
-    e = cudaMemcpy(h->valid, tmp, h->batch, cudaMemcpyHostToDevice);
-  }
-  delete[] tmp;
-  CK(e);
+  invalidate_kernel<<<(h->batch + 255) / 256, 256, 0, h->stream>>>(h->valid, dmask, h->batch);
+  h->launches++;
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(h->stream));
   return NMPC_OK;
 }
 
@@ -411,7 +470,7 @@ static int launch_solve(nmpc_handle* h, const double* x0, const double* yref, co
                         double* u0, int32_t* status, double* thrust, double* speed,
                         cudaStream_t st) {
   SolveArgs<T> A;
-  A.cfg = make_devcfg<T>(h->cfg);
+  A.cfg = devcfg_of<T>(h);
   A.batch = h->batch;
   A.x0 = x0;
   A.yref = yref;
@@ -430,11 +489,14 @@ static int launch_solve(nmpc_handle* h, const double* x0, const double* yref, co
   // bulk copies need 16-byte aligned sources: the caller's yref may not be (then direct loads)
   A.stage = (h->stage_bytes > 0 && (reinterpret_cast<uintptr_t>(yref) & 15) == 0) ? 1 : 0;
   const size_t smem = solve_smem_bytes<T>(h);
+  // one workspace per handle: a solve on another stream than the previous one queues behind it
+  CK(cudaStreamWaitEvent(st, h->ev_last, 0));
   CK(cudaMemsetAsync(h->counter, 0, sizeof(int), st));
   nmpc_solve_kernel<T, NS, NF>
       <<<h->grid, WARPS * 32, smem, st>>>(A, h->L, h->counter);
   h->launches++;
   CK(cudaGetLastError());
+  mark_enqueued(h, st);
   return NMPC_OK;
 }
 
@@ -489,12 +551,14 @@ int nmpc_get_trajectories(nmpc_handle_t* h, double* xtraj, double* utraj, uint8_
                           int32_t dst_is_device) {
   if (!h) return NMPC_E_INVALID;
   CK(cudaSetDevice(h->device));
-  CK(cudaDeviceSynchronize());
+  CK(order_behind_last(h));
   const size_t B = h->batch, N = h->cfg.N;
   const cudaMemcpyKind kind = dst_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
-  if (xtraj) CK(cudaMemcpy(xtraj, h->xtraj, B * (N + 1) * NX * sizeof(double), kind));
-  if (utraj) CK(cudaMemcpy(utraj, h->utraj, B * N * NU * sizeof(double), kind));
-  if (valid) CK(cudaMemcpy(valid, h->valid, B, kind));
+  cudaStream_t st = h->stream;
+  if (xtraj) CK(cudaMemcpyAsync(xtraj, h->xtraj, B * (N + 1) * NX * sizeof(double), kind, st));
+  if (utraj) CK(cudaMemcpyAsync(utraj, h->utraj, B * N * NU * sizeof(double), kind, st));
+  if (valid) CK(cudaMemcpyAsync(valid, h->valid, B, kind, st));
+  CK(cudaStreamSynchronize(st));
   return NMPC_OK;
 }
 
@@ -502,12 +566,16 @@ int nmpc_set_trajectories(nmpc_handle_t* h, const double* xtraj, const double* u
                           const uint8_t* valid) {
   if (!h) return NMPC_E_INVALID;
   CK(cudaSetDevice(h->device));
-  CK(cudaDeviceSynchronize());
+  CK(order_behind_last(h));
   const size_t B = h->batch, N = h->cfg.N;
+  cudaStream_t st = h->stream;
   if (xtraj)
-    CK(cudaMemcpy(h->xtraj, xtraj, B * (N + 1) * NX * sizeof(double), cudaMemcpyHostToDevice));
-  if (utraj) CK(cudaMemcpy(h->utraj, utraj, B * N * NU * sizeof(double), cudaMemcpyHostToDevice));
-  if (valid) CK(cudaMemcpy(h->valid, valid, B, cudaMemcpyHostToDevice));
+    CK(cudaMemcpyAsync(h->xtraj, xtraj, B * (N + 1) * NX * sizeof(double), cudaMemcpyHostToDevice,
+                       st));
+  if (utraj)
+    CK(cudaMemcpyAsync(h->utraj, utraj, B * N * NU * sizeof(double), cudaMemcpyHostToDevice, st));
+  if (valid) CK(cudaMemcpyAsync(h->valid, valid, B, cudaMemcpyHostToDevice, st));
+  CK(cudaStreamSynchronize(st));
   return NMPC_OK;
 }
 
@@ -515,11 +583,13 @@ int nmpc_get_stats(nmpc_handle_t* h, int32_t* qp_iters, int32_t* sqp_iters,
                    int32_t dst_is_device) {
   if (!h) return NMPC_E_INVALID;
   CK(cudaSetDevice(h->device));
-  CK(cudaDeviceSynchronize());
+  CK(order_behind_last(h));
   const size_t B = h->batch;
   const cudaMemcpyKind kind = dst_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
-  if (qp_iters) CK(cudaMemcpy(qp_iters, h->qp_iters, B * sizeof(int), kind));
-  if (sqp_iters) CK(cudaMemcpy(sqp_iters, h->sqp_iters, B * sizeof(int), kind));
+  cudaStream_t st = h->stream;
+  if (qp_iters) CK(cudaMemcpyAsync(qp_iters, h->qp_iters, B * sizeof(int), kind, st));
+  if (sqp_iters) CK(cudaMemcpyAsync(sqp_iters, h->sqp_iters, B * sizeof(int), kind, st));
+  CK(cudaStreamSynchronize(st));
   return NMPC_OK;
 }
 
@@ -527,7 +597,7 @@ extern "C++" {
 template <typename T>
 static int launch_disc(nmpc_handle* h, int n, const double* x, const double* u, double* xn,
                        double* A, double* B, cudaStream_t st) {
-  DevCfg<T> c = make_devcfg<T>(h->cfg);
+  const DevCfg<T>& c = devcfg_of<T>(h);
   const int grid = (n + WARPS - 1) / WARPS;
   switch (h->cfg.integ_ns) {
     case 1: nmpc_discretize_kernel<T, 1><<<grid, WARPS * 32, 0, st>>>(c, n, x, u, xn, A, B); break;
@@ -622,13 +692,14 @@ static int launch_plant(nmpc_handle* h, const nmpc_plant_t* plant, double* x, do
                         const double* thrust, double* rotor_speed, const double* pref,
                         size_t pref_stride, const int32_t* status, const int32_t* qp_iters,
                         double* stats, cudaStream_t st) {
-  const DevCfg<double> c = make_devcfg<double>(h->cfg);
+  const DevCfg<double>& c = h->dc64;
   const PlantCfg pc = make_plantcfg(h, *plant);
   plant_step_kernel<<<(h->batch + 127) / 128, 128, 0, st>>>(c, pc, h->batch, x, x0, thrust,
                                                             rotor_speed, pref, pref_stride, status,
                                                             qp_iters, stats);
   h->launches++;
   CK(cudaGetLastError());
+  mark_enqueued(h, st);
   return NMPC_OK;
 }
 

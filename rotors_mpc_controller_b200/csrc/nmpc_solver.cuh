@@ -7,12 +7,15 @@
 // tree); the algorithm is the textbook stage-wise Riccati recursion inside a Mehrotra
 // predictor-corrector, laid out for one warp:
 //
-//   lane j (0..16) owns COLUMN j of the stage matrix M_k = [B_k | A_k] (13 x 17) and of every
-//   matrix derived from it (W = P M, G = M' W), kept in registers; the 13x13 cost-to-go P,
-//   the staged M_k and the feedback K_k are broadcast through a 4 KB per-warp shared-memory
-//   tile; 4x4 input blocks are exchanged with warp shuffles and factorised redundantly.
-//   Per-stage factors (K, Quu^-1, k) and all horizon-long vectors live in an L2-resident
-//   global workspace slot owned by the warp (sized by N, so N = 600 runs unchanged).
+//   K1 linearise: lane = one sensitivity column of M_k = [B_k | A_k] (14 computed columns, the
+//      two half-warps take two stages at a time); no Jacobian matrix is formed.
+//   K2 factorisation: both half-warps own the 14 computed columns and split the ROWS of
+//      W = P M, G = M'W and of the cost-to-go update (see nmpc_riccati.cuh); P, the cp.async-staged
+//      M_k, K_k and the 4x4 input block go through a per-warp shared-memory tile.
+//   Roll-outs: lanes 0..12 own the rows of M_k, lanes 16..19 the rows of K_k.
+//   Per-stage records [M_k | b_k | K_k], LDL' factors, feed-forwards and all horizon-long
+//   vectors live in a global workspace slot owned by the warp (sized by N, so N = 600 runs
+//   unchanged); per-problem inputs are staged by 1-D TMA bulk copies.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -660,9 +663,12 @@ __device__ __forceinline__ void load_inputs(const SolveArgs<T>& A, const WsLayou
     void* bar = sm + SmemLayout::bar;
     const size_t xoff = (size_t)prob * nxv * sizeof(double);
     const unsigned mis = (unsigned)(xoff & 15);
+    // the tile was last written through the generic proxy by ALL lanes (sweeps of the previous
+    // problem): every writer fences its own generic-proxy writes against the async proxy, then the
+    // warp converges, then lane 0 arms the barrier and issues the copies
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncwarp();
     if (lane == 0) {
-      // the tile was last written through the generic proxy (sweeps of the previous problem)
-      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       mbar_expect_tx(bar, (unsigned)(S.ybytes + S.ubytes + S.xbytes));
       tma_load_1d(ybuf, yref, (unsigned)S.ybytes, bar);
       tma_load_1d(ubuf, u_in, (unsigned)S.ubytes, bar);

@@ -18,7 +18,7 @@ sys.path.insert(0, str(ROOT))
 from oracle import oracle as O  # noqa: E402
 from tests.problems import aggressive, random_states, setpoint_refs  # noqa: E402
 
-FLAGS = dict(integ_ns=2, integ_steps=2, cost_scale_dt=1, lm_scaled_by_dt=0, max_sqp_iter=1,
+FLAGS = dict(integ_ns=2, integ_steps=2, cost_scale_dt=1, lm_scaled_by_dt=1, max_sqp_iter=1,
              ipm_tol=1e-14, nan_status=4, bounds='kf*w^2 -> [0.02137145, 6.00318901] N')
 
 

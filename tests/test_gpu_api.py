@@ -145,6 +145,52 @@ def test_masked_invalidate_and_store_round_trip(params, O):
     twin.close()
 
 
+def test_device_mask_invalidate_and_stream_scope(params, O):
+    """nmpc_invalidate_device: a device mask on the caller's stream, no host synchronisation.
+    nmpc_invalidate / nmpc_get_* are stream-scoped: they wait for THEIR handle's last kernel
+    only, so a long solve in flight on another handle's stream is not waited for."""
+    import time
+
+    import torch
+    dev = torch.device('cuda', 0)
+    B = 64
+    ctl = _ctl(params, B)
+    rng = np.random.default_rng(11)
+    x0 = random_states(rng, B)
+    yref, yref_e = setpoint_refs(rng, x0, 20, ctl.hover_thrust)
+    ctl.solve(x0, yref, yref_e)
+    mask = torch.as_tensor((np.arange(B) % 4 == 1).astype(np.uint8), device=dev)
+    ctl.invalidate(mask)                                   # device mask, async
+    valid = ctl.trajectories()[2]                          # ordered behind the kernel
+    assert np.array_equal(valid, np.arange(B) % 4 != 1)
+    with pytest.raises(ValueError):
+        ctl.invalidate(torch.zeros(B + 1, dtype=torch.uint8, device=dev))
+    # a long SQP solve on another handle / another stream ...
+    p = copy.deepcopy(params)
+    p['solver'].update(max_sqp_iter=50, sqp_tol=1e-8)
+    from rotors_mpc_controller_b200 import BatchedPositionNMPC
+    big = BatchedPositionNMPC(p, batch=16384)
+    xb = random_states(rng, 16384)
+    yb, yeb = setpoint_refs(rng, xb, 20, big.hover_thrust)
+    xb, yb, yeb = (torch.as_tensor(a, device=dev) for a in (xb, yb, yeb))
+    side = torch.cuda.Stream(dev)
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter()
+    with torch.cuda.stream(side):
+        big.solve(xb, yb, yeb)
+    # ... does not serialise the small handle's host-side calls
+    ctl.invalidate(np.ones(B, np.uint8))
+    ctl.invalidate()
+    ctl.stats()
+    t_small = time.perf_counter() - t0
+    side.synchronize()
+    t_big = time.perf_counter() - t0
+    assert not ctl.trajectories()[2].any()
+    assert t_small < 0.5 * t_big, (t_small, t_big)
+    big.close()
+    ctl.close()
+
+
 def test_abi_error_codes(params, built):
     """Every entry point answers a bad argument with NMPC_E_INVALID instead of crashing; a
     per-problem solver failure is data (status), never an error code."""
