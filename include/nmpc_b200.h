@@ -229,6 +229,13 @@ int nmpc_last_outputs(nmpc_handle_t *h, const double **u0, const int32_t **statu
  * best of 4): the FP64 roofline denominator used by bench.py. */
 int nmpc_fp64_peak(int32_t device, double *tflops);
 
+/* Debug aid standing in for compute-sanitizer's initcheck (the tool is closed on this GPU pool):
+ * with `on`, every launch first fills the whole workspace with NaN and the kernel fills its
+ * shared-memory tile with NaN before every problem, so a read of anything the problem has not
+ * written itself poisons its results.  Results must be bit-identical with and without it
+ * (tests/test_gpu_api.py::test_poisoned_memory_changes_nothing). */
+int nmpc_debug_poison(nmpc_handle_t *h, int32_t on);
+
 /* Introspection */
 int nmpc_batch(const nmpc_handle_t *h);
 int nmpc_horizon(const nmpc_handle_t *h);

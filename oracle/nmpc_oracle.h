@@ -64,6 +64,12 @@ typedef struct {
   int nan_status;     /* status reported when NaNs appear (4 = QP failure, or 1) */
   int ipm_warm;       /* 1: QPs after the first of an SQP run (max_sqp_iter > 1) warm-start the
                          interior point from the previous QP's (t, lam), see ORC_WARM_* */
+  int keep_state_box; /* 1: the +-state_box rows on all 13 states at stages 1..N-1
+                         (controller.py:257-261) are real inequality rows of the QP, as in the
+                         reference's HPIPM problem.  ORACLE-ONLY sensitivity flag (default 0): the
+                         rows are never active, they only perturb the interior-point iterates --
+                         scripts/flag_sensitivity.py measures by how much.  Disables ipm_warm. */
+  double state_box;   /* 1e6 (controller.py:258) */
 } orc_config;
 
 /* Warm start between the QPs of one SQP run: used when the previous QP's interior-point loop
@@ -103,6 +109,9 @@ typedef struct {
   double *r;   /* N*4 */
   double *lb;  /* N*4   lbu - ubar */
   double *ub;  /* N*4 */
+  double *lbx; /* (N+1)*13  -state_box - xbar (rows of stages 1..N-1 used when xbox) */
+  double *ubx; /* (N+1)*13 */
+  int xbox;    /* state box rows present (orc_config.keep_state_box) */
 } orc_qp;
 
 orc_qp *orc_qp_alloc(int N);

@@ -30,6 +30,9 @@ orc_qp *orc_qp_alloc(int N) {
   qp->r = (double *)calloc((size_t)N * NU, sizeof(double));
   qp->lb = (double *)calloc((size_t)N * NU, sizeof(double));
   qp->ub = (double *)calloc((size_t)N * NU, sizeof(double));
+  qp->lbx = (double *)calloc((size_t)(N + 1) * NX, sizeof(double));
+  qp->ubx = (double *)calloc((size_t)(N + 1) * NX, sizeof(double));
+  qp->xbox = 0;
   return qp;
 }
 
@@ -44,6 +47,8 @@ void orc_qp_free(orc_qp *qp) {
   free(qp->r);
   free(qp->lb);
   free(qp->ub);
+  free(qp->lbx);
+  free(qp->ubx);
   free(qp);
 }
 
@@ -76,6 +81,14 @@ void orc_build_qp(const orc_config *c, const double *xtraj, const double *utraj,
     qp->Q[N * NX + i] = c->We[i] + c->lm;
     qp->q[N * NX + i] = c->We[i] * (xN[i] - yref_e[i]);
   }
+  /* controller.py:257-261: lbx = -1e6, ubx = +1e6 on every state, stages 1..N-1 */
+  qp->xbox = c->keep_state_box ? 1 : 0;
+  if (qp->xbox)
+    for (int k = 1; k < N; k++)
+      for (int i = 0; i < NX; i++) {
+        qp->lbx[k * NX + i] = -c->state_box - xtraj[(size_t)k * NX + i];
+        qp->ubx[k * NX + i] = c->state_box - xtraj[(size_t)k * NX + i];
+      }
 }
 
 /* ---------------------------------------------------------------- Riccati */
@@ -121,13 +134,17 @@ static int chol4_inv(const double *G, double *Ginv) {
 
 /* Backward factorisation with modified input Hessian Rt and gradient rt, fused with the
  * right-hand side (rho*b, rho*q, rt); forward roll-out from dx_0 = 0.  Returns non-zero on breakdown. */
-static int riccati_factor_solve(const orc_qp *qp, double rho, const double *Rt, const double *rt,
-                                ric_ws *ws, double *dx, double *du) {
+static int riccati_factor_solve(const orc_qp *qp, double rho, const double *Qt, const double *qt,
+                                const double *Rt, const double *rt, ric_ws *ws, double *dx,
+                                double *du) {
+  /* Qt / qt: state Hessian diagonal and state gradient ((N+1)*13 each).  Without state-box rows
+   * they are the plain data Q and rho*q; with them (keep_state_box) they carry the barrier terms
+   * of those rows exactly like Rt / rt do for the input box. */
   const int N = qp->N;
   double P[NX * NX] = {0}, p[NX];
   for (int i = 0; i < NX; i++) {
-    P[i * NX + i] = qp->Q[N * NX + i];
-    p[i] = rho * qp->q[N * NX + i];
+    P[i * NX + i] = Qt[N * NX + i];
+    p[i] = qt[N * NX + i];
   }
   for (int k = N - 1; k >= 0; k--) {
     const double *A = qp->A + (size_t)k * NX * NX;
@@ -167,11 +184,11 @@ static int riccati_factor_solve(const orc_qp *qp, double rho, const double *Rt, 
     }
     for (int i = 0; i < NX; i++) {
       for (int j = 0; j < NX; j++) {
-        double s = (i == j) ? qp->Q[k * NX + i] : 0.0;
+        double s = (i == j) ? Qt[k * NX + i] : 0.0;
         for (int l = 0; l < NX; l++) s += A[l * NX + i] * PA[l * NX + j];
         Qxx[i * NX + j] = s;
       }
-      double s = rho * qp->q[k * NX + i];
+      double s = qt[k * NX + i];
       for (int l = 0; l < NX; l++) s += A[l * NX + i] * w[l];
       gx[i] = s;
     }
@@ -231,8 +248,8 @@ static int riccati_factor_solve(const orc_qp *qp, double rho, const double *Rt, 
 
 /* Re-solve with the same factorisation for a right-hand side that differs only in the
  * input gradient (b = 0, q = 0, r = dr): the corrector increment of Mehrotra's method. */
-static void riccati_delta_solve(const orc_qp *qp, const double *dr, const ric_ws *ws, double *dx,
-                                double *du, double *kffd) {
+static void riccati_delta_solve(const orc_qp *qp, const double *dr, const double *dq,
+                                const ric_ws *ws, double *dx, double *du, double *kffd) {
   const int N = qp->N;
   double p[NX] = {0};
   for (int k = N - 1; k >= 0; k--) {
@@ -247,7 +264,7 @@ static void riccati_delta_solve(const orc_qp *qp, const double *dr, const ric_ws
       gu[i] = s;
     }
     for (int i = 0; i < NX; i++) {
-      double s = 0;
+      double s = dq ? dq[k * NX + i] : 0.0; /* state-box rows (keep_state_box) */
       for (int l = 0; l < NX; l++) s += A[l * NX + i] * p[l];
       gx[i] = s;
     }
@@ -325,17 +342,28 @@ int orc_qp_solve_warm(const orc_qp *qp, int iter_max, double tol, double *dx, do
                       int *ipm_converged, int *iters) {
   const int N = qp->N;
   const int nb = N * NU;
+  const int nxv = (N + 1) * NX;
+  /* state-box rows (keep_state_box): rows k*13+i for k = 1..N-1; the others are masked out */
+  const int xbox = qp->xbox;
+  const int xlo = NX, xhi = N * NX; /* [xlo, xhi) = stages 1..N-1 */
+  const int nbx = (xbox && xhi > xlo) ? (xhi - xlo) : 0;
   ric_ws ws;
   ws.N = N;
   ws.K = (double *)malloc(sizeof(double) * (size_t)N * NU * NX);
   ws.Qi = (double *)malloc(sizeof(double) * (size_t)N * 16);
   ws.kff = (double *)malloc(sizeof(double) * (size_t)N * NU);
-  double *buf = (double *)calloc((size_t)nb * 15 + (size_t)(N + 1) * NX * 2, sizeof(double));
+  double *buf = (double *)calloc((size_t)nb * 15 + (size_t)nxv * 16, sizeof(double));
   double *t_l = buf, *t_u = t_l + nb, *Rt = t_u + nb, *rt = Rt + nb;
   double *dtl = rt + nb, *dtu = dtl + nb, *dll = dtu + nb, *dlu = dll + nb;
   double *dr = dlu + nb, *ua = dr + nb, *uc = ua + nb, *kffd = uc + nb;
   double *rbl0 = kffd + nb, *rbu0 = rbl0 + nb, *ru0 = rbu0 + nb;
-  double *xa = ru0 + nb, *xc = xa + (size_t)(N + 1) * NX;
+  double *xa = ru0 + nb, *xc = xa + nxv;
+  /* state rows: Hessian diagonal / gradient handed to the Riccati solve, slacks, multipliers,
+   * their directions, corrector gradient, initial residuals */
+  double *Qt = xc + nxv, *qt = Qt + nxv, *dq = qt + nxv;
+  double *s_l = dq + nxv, *s_u = s_l + nxv, *m_l = s_u + nxv, *m_u = m_l + nxv;
+  double *dsl = m_u + nxv, *dsu = dsl + nxv, *dml = dsu + nxv, *dmu = dml + nxv;
+  double *rxl0 = dmu + nxv, *rxu0 = rxl0 + nxv, *rx0 = rxu0 + nxv;
   int status = ORC_MAXITER;
   int it = 0;
   if (ipm_converged) *ipm_converged = 0;
@@ -345,7 +373,7 @@ int orc_qp_solve_warm(const orc_qp *qp, int iter_max, double tol, double *dx, do
   double res0 = 0.0;
   for (int i = 0; i < nb; i++) res0 = fmax(res0, fabs(qp->r[i]) + fabs(qp->lb[i]) + fabs(qp->ub[i]));
   for (int i = 0; i < N * NX; i++) res0 = fmax(res0, fabs(qp->b[i]));
-  for (int i = 0; i < (N + 1) * NX; i++) res0 = fmax(res0, fabs(qp->q[i]));
+  for (int i = 0; i < nxv; i++) res0 = fmax(res0, fabs(qp->q[i]));
   if (!(res0 == res0) || isinf(res0)) { /* NaN/Inf in the QP data */
     status = ORC_QP_FAILURE;
     goto done;
@@ -357,9 +385,9 @@ int orc_qp_solve_warm(const orc_qp *qp, int iter_max, double tol, double *dx, do
   const double rq = skip0 ? 1.0 : 0.0;
   if (skip0) {
     for (int i = 0; i < nb; i++) du[i] = 0.0;
-    for (int i = 0; i < (N + 1) * NX; i++) dx[i] = 0.0;
+    for (int i = 0; i < nxv; i++) dx[i] = 0.0;
   } else {
-    if (riccati_factor_solve(qp, 1.0, qp->R, qp->r, &ws, dx, du)) {
+    if (riccati_factor_solve(qp, 1.0, qp->Q, qp->q, qp->R, qp->r, &ws, dx, du)) {
       status = ORC_QP_FAILURE;
       goto done;
     }
@@ -369,6 +397,8 @@ int orc_qp_solve_warm(const orc_qp *qp, int iter_max, double tol, double *dx, do
     int feasible = 1;
     for (int i = 0; i < nb; i++)
       if (!(du[i] >= qp->lb[i] && du[i] <= qp->ub[i])) feasible = 0;
+    for (int i = xlo; i < xlo + nbx; i++)
+      if (!(dx[i] >= qp->lbx[i] && dx[i] <= qp->ubx[i])) feasible = 0;
     if (feasible) {
       for (int i = 0; i < nb; i++) lam_l[i] = lam_u[i] = 0.0;
       status = ORC_SUCCESS;
@@ -397,16 +427,30 @@ int orc_qp_solve_warm(const orc_qp *qp, int iter_max, double tol, double *dx, do
     res0 = fmax(res0, fmax(fabs(rbl0[i]), fabs(rbu0[i])));
     res0 = fmax(res0, fabs(ru0[i]));
   }
+  for (int i = 0; i < nxv; i++) rx0[i] = rq * qp->q[i];
+  for (int i = xlo; i < xlo + nbx; i++) { /* same start rule for the state rows (never warm) */
+    s_l[i] = fmax(dx[i] - qp->lbx[i], thr0);
+    s_u[i] = fmax(qp->ubx[i] - dx[i], thr0);
+    m_l[i] = mu0 / s_l[i];
+    m_u[i] = mu0 / s_u[i];
+    rxl0[i] = dx[i] - qp->lbx[i] - s_l[i];
+    rxu0[i] = qp->ubx[i] - dx[i] - s_u[i];
+    rx0[i] += -m_l[i] + m_u[i];
+    res0 = fmax(res0, fmax(fabs(rxl0[i]), fabs(rxu0[i])));
+    res0 = fmax(res0, fabs(rx0[i]));
+  }
   double rho = 1.0;
   if (skip0) {
     for (int i = 0; i < N * NX; i++) res0 = fmax(res0, fabs(qp->b[i]));
-    for (int i = 0; i < (N + 1) * NX; i++) res0 = fmax(res0, fabs(qp->q[i]));
+    for (int i = 0; i < nxv; i++) res0 = fmax(res0, fabs(qp->q[i]));
   }
+  const double inv_rows = 1.0 / (double)(2 * nb + 2 * nbx);
 
   for (; it < iter_max; it++) {
     double mu = 0.0;
     for (int i = 0; i < nb; i++) mu += t_l[i] * lam_l[i] + t_u[i] * lam_u[i];
-    mu /= (double)(2 * nb);
+    for (int i = xlo; i < xlo + nbx; i++) mu += s_l[i] * m_l[i] + s_u[i] * m_u[i];
+    mu *= inv_rows;
     if (!(mu == mu)) {
       status = ORC_QP_FAILURE;
       break;
@@ -421,7 +465,16 @@ int orc_qp_solve_warm(const orc_qp *qp, int iter_max, double tol, double *dx, do
       Rt[i] = qp->R[i] + dl + dw;
       rt[i] = rho * ru0[i] + dl * (rho * rbl0[i]) + lam_l[i] - dw * (rho * rbu0[i]) - lam_u[i];
     }
-    if (riccati_factor_solve(qp, rq * rho, Rt, rt, &ws, xa, ua)) {
+    for (int i = 0; i < nxv; i++) {
+      Qt[i] = qp->Q[i];
+      qt[i] = rho * rx0[i];
+    }
+    for (int i = xlo; i < xlo + nbx; i++) {
+      const double dl = m_l[i] / s_l[i], dw = m_u[i] / s_u[i];
+      Qt[i] += dl + dw;
+      qt[i] += dl * (rho * rxl0[i]) + m_l[i] - dw * (rho * rxu0[i]) - m_u[i];
+    }
+    if (riccati_factor_solve(qp, rq * rho, Qt, qt, Rt, rt, &ws, xa, ua)) {
       status = ORC_QP_FAILURE;
       break;
     }
@@ -436,21 +489,39 @@ int orc_qp_solve_warm(const orc_qp *qp, int iter_max, double tol, double *dx, do
       if (dll[i] < 0) alpha_aff = fmin(alpha_aff, -lam_l[i] / dll[i]);
       if (dlu[i] < 0) alpha_aff = fmin(alpha_aff, -lam_u[i] / dlu[i]);
     }
+    for (int i = xlo; i < xlo + nbx; i++) {
+      dsl[i] = xa[i] + rho * rxl0[i];
+      dsu[i] = -xa[i] + rho * rxu0[i];
+      dml[i] = -(m_l[i] / s_l[i]) * dsl[i] - m_l[i];
+      dmu[i] = -(m_u[i] / s_u[i]) * dsu[i] - m_u[i];
+      if (dsl[i] < 0) alpha_aff = fmin(alpha_aff, -s_l[i] / dsl[i]);
+      if (dsu[i] < 0) alpha_aff = fmin(alpha_aff, -s_u[i] / dsu[i]);
+      if (dml[i] < 0) alpha_aff = fmin(alpha_aff, -m_l[i] / dml[i]);
+      if (dmu[i] < 0) alpha_aff = fmin(alpha_aff, -m_u[i] / dmu[i]);
+    }
     double mu_aff = 0.0;
     for (int i = 0; i < nb; i++)
       mu_aff += (t_l[i] + alpha_aff * dtl[i]) * (lam_l[i] + alpha_aff * dll[i]) +
                 (t_u[i] + alpha_aff * dtu[i]) * (lam_u[i] + alpha_aff * dlu[i]);
-    mu_aff /= (double)(2 * nb);
+    for (int i = xlo; i < xlo + nbx; i++)
+      mu_aff += (s_l[i] + alpha_aff * dsl[i]) * (m_l[i] + alpha_aff * dml[i]) +
+                (s_u[i] + alpha_aff * dsu[i]) * (m_u[i] + alpha_aff * dmu[i]);
+    mu_aff *= inv_rows;
     double sigma = mu_aff / mu;
     sigma = sigma * sigma * sigma;
     const double CORRW = corr_weight(alpha_aff);
-    /* corrector increment: only the input gradient changes */
+    /* corrector increment: only the box-row gradients change */
     for (int i = 0; i < nb; i++) {
       const double sl = sigma * mu - CORRW * dtl[i] * dll[i];
       const double su = sigma * mu - CORRW * dtu[i] * dlu[i];
       dr[i] = -sl / t_l[i] + su / t_u[i];
     }
-    riccati_delta_solve(qp, dr, &ws, xc, uc, kffd);
+    for (int i = xlo; i < xlo + nbx; i++) {
+      const double sl = sigma * mu - CORRW * dsl[i] * dml[i];
+      const double su = sigma * mu - CORRW * dsu[i] * dmu[i];
+      dq[i] = -sl / s_l[i] + su / s_u[i];
+    }
+    riccati_delta_solve(qp, dr, nbx ? dq : NULL, &ws, xc, uc, kffd);
     double alpha = 1e300; /* longest step keeping t, lam >= 0 (not capped at 1 yet) */
     for (int i = 0; i < nb; i++) {
       const double un = ua[i] + uc[i];
@@ -465,18 +536,22 @@ int orc_qp_solve_warm(const orc_qp *qp, int iter_max, double tol, double *dx, do
       if (dll[i] < 0) alpha = fmin(alpha, -lam_l[i] / dll[i]);
       if (dlu[i] < 0) alpha = fmin(alpha, -lam_u[i] / dlu[i]);
     }
-#ifdef ORC_TRACE
-    {
-      double tmin = 1e300, lmin = 1e300, cmin = 1e300, cmax = 0;
-      for (int i = 0; i < nb; i++) {
-        tmin = fmin(tmin, fmin(t_l[i], t_u[i]));
-        lmin = fmin(lmin, fmin(lam_l[i], lam_u[i]));
-        cmin = fmin(cmin, fmin(t_l[i] * lam_l[i], t_u[i] * lam_u[i]));
-        cmax = fmax(cmax, fmax(t_l[i] * lam_l[i], t_u[i] * lam_u[i]));
-      }
-      fprintf(stderr, "it %d mu %.3e mu_aff %.3e sig %.2e a_aff %.2e amax %.3e rho %.2e tmin %.1e lmin %.1e cmin %.1e cmax %.1e\n",
-              it, mu, mu_aff, sigma, alpha_aff, alpha, rho, tmin, lmin, cmin, cmax);
+    for (int i = xlo; i < xlo + nbx; i++) {
+      const double xn = xa[i] + xc[i];
+      const double sl = sigma * mu - CORRW * dsl[i] * dml[i];
+      const double su = sigma * mu - CORRW * dsu[i] * dmu[i];
+      dsl[i] = xn + rho * rxl0[i];
+      dsu[i] = -xn + rho * rxu0[i];
+      dml[i] = -(m_l[i] / s_l[i]) * dsl[i] + sl / s_l[i] - m_l[i];
+      dmu[i] = -(m_u[i] / s_u[i]) * dsu[i] + su / s_u[i] - m_u[i];
+      if (dsl[i] < 0) alpha = fmin(alpha, -s_l[i] / dsl[i]);
+      if (dsu[i] < 0) alpha = fmin(alpha, -s_u[i] / dsu[i]);
+      if (dml[i] < 0) alpha = fmin(alpha, -m_l[i] / dml[i]);
+      if (dmu[i] < 0) alpha = fmin(alpha, -m_u[i] / dmu[i]);
     }
+#ifdef ORC_TRACE
+    fprintf(stderr, "it %d mu %.3e mu_aff %.3e sig %.2e a_aff %.2e amax %.3e rho %.2e\n", it, mu,
+            mu_aff, sigma, alpha_aff, alpha, rho);
 #endif
     if (!(alpha == alpha)) {
       status = ORC_QP_FAILURE;
@@ -496,7 +571,13 @@ int orc_qp_solve_warm(const orc_qp *qp, int iter_max, double tol, double *dx, do
       lam_l[i] += alpha * dll[i];
       lam_u[i] += alpha * dlu[i];
     }
-    for (int i = 0; i < (N + 1) * NX; i++) dx[i] += alpha * (xa[i] + xc[i]);
+    for (int i = xlo; i < xlo + nbx; i++) {
+      s_l[i] += alpha * dsl[i];
+      s_u[i] += alpha * dsu[i];
+      m_l[i] += alpha * dml[i];
+      m_u[i] += alpha * dmu[i];
+    }
+    for (int i = 0; i < nxv; i++) dx[i] += alpha * (xa[i] + xc[i]);
     rho *= (1.0 - alpha);
   }
   if (t_l_io && t_u_io) {

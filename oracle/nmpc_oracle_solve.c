@@ -52,7 +52,7 @@ int orc_solve(const orc_config *c, const double *x0, const double *yref, const d
     orc_build_qp(c, xb, ub, yref, yref_e, qp);
     int qi = 0;
     double weps = 0.0;
-    if (c->ipm_warm && have_ipm && prev_step <= ORC_WARM_STEP_MAX)
+    if (c->ipm_warm && !c->keep_state_box && have_ipm && prev_step <= ORC_WARM_STEP_MAX)
       weps = fmin(fmax(ORC_WARM_KAPPA * prev_step, ORC_WARM_EPS_MIN), ORC_WARM_EPS_MAX);
     const int qs = orc_qp_solve_warm(qp, c->qp_iter_max, c->ipm_tol, dx, du, ll, lu, tl, tu, weps,
                                      &have_ipm, &qi);

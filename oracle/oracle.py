@@ -33,13 +33,14 @@ class OrcConfig(C.Structure):
         ('w_max', C.c_double), ('integ_ns', C.c_int), ('integ_steps', C.c_int),
         ('cost_scale_dt', C.c_int), ('lm_scaled_by_dt', C.c_int), ('max_sqp_iter', C.c_int),
         ('sqp_tol', C.c_double), ('ipm_tol', C.c_double), ('nan_status', C.c_int),
-        ('ipm_warm', C.c_int),
+        ('ipm_warm', C.c_int), ('keep_state_box', C.c_int), ('state_box', C.c_double),
     ]
 
 
 class OrcQP(C.Structure):
-    _fields_ = [('N', C.c_int)] + [(n, C.POINTER(C.c_double))
-                                   for n in ('A', 'B', 'b', 'Q', 'R', 'q', 'r', 'lb', 'ub')]
+    _fields_ = ([('N', C.c_int)] + [(n, C.POINTER(C.c_double))
+                                    for n in ('A', 'B', 'b', 'Q', 'R', 'q', 'r', 'lb', 'ub',
+                                              'lbx', 'ubx')] + [('xbox', C.c_int)])
 
 
 def build(force: bool = False) -> Path:
@@ -127,6 +128,8 @@ def config_from_params(params: Dict[str, Dict[str, object]], **flags) -> OrcConf
     c.ipm_tol = float(flags.get('ipm_tol', 1e-14))
     c.nan_status = int(flags.get('nan_status', 4))
     c.ipm_warm = int(bool(flags.get('ipm_warm', s.get('ipm_warm_start', True))))
+    c.keep_state_box = int(flags.get('keep_state_box', 0))   # controller.py:257-261 (oracle-only)
+    c.state_box = float(flags.get('state_box', 1.0e6))
     return c
 
 
@@ -169,6 +172,9 @@ def build_qp(cfg, xtraj, utraj, yref, yref_e) -> Dict[str, np.ndarray]:
                r=(N, NU), lb=(N, NU), ub=(N, NU))
     out = {k: np.ctypeslib.as_array(getattr(qp.contents, k), shape=s).copy()
            for k, s in shp.items()}
+    if qp.contents.xbox:
+        for k in ('lbx', 'ubx'):
+            out[k] = np.ctypeslib.as_array(getattr(qp.contents, k), shape=(N + 1, NX)).copy()
     lib().orc_qp_free(qp)
     return out
 
@@ -181,6 +187,10 @@ def qp_solve(qpd: Dict[str, np.ndarray], iter_max=600, tol=1e-14):
                                                               'lb', 'ub')}
     for k, a in keep.items():
         setattr(qp, k, _p(a))
+    if 'lbx' in qpd:      # state-box rows (keep_state_box)
+        keep['lbx'] = np.ascontiguousarray(qpd['lbx'], float)
+        keep['ubx'] = np.ascontiguousarray(qpd['ubx'], float)
+        qp.lbx, qp.ubx, qp.xbox = _p(keep['lbx']), _p(keep['ubx']), 1
     dx, du = np.zeros((N + 1, NX)), np.zeros((N, NU))
     ll, lu = np.zeros((N, NU)), np.zeros((N, NU))
     it = C.c_int(0)

@@ -1,6 +1,9 @@
 """Independent checks for the oracle's QP solve (test infrastructure, NOT the product).
 
-Two things that do not share code with the Riccati interior-point method:
+Three things that do not share code with the Riccati interior-point method:
+  * ``active_set_kkt`` -- for a GIVEN active set, the equality-constrained KKT system solved
+    densely (numpy ``solve`` on the condensed Hessian): the exact vertex the interior point
+    converges to, with its multipliers;
   * ``condensed_active_set`` -- eliminates the states (dense condensing, numpy) and solves the
     resulting 4N-variable box QP with scipy's BVLS active-set method to machine precision;
   * ``kkt_residuals`` -- stationarity / dynamics / complementarity residuals of a candidate
@@ -54,6 +57,28 @@ def condensed_active_set(qp, max_iter=None):
     N = qp['A'].shape[0]
     dx = np.einsum('kij,j->ki', G, U) + c
     return dx, U.reshape(N, NU)
+
+
+def active_set_kkt(qp, act_l, act_u):
+    """Exact solution for a given active set: inputs with act_l / act_u (N x 4 boolean) sit on
+    their lower / upper bound, the others solve the reduced stationarity system directly.
+    Returns (dx, du, lam_l, lam_u); the active set is the optimal one iff du is feasible and the
+    multipliers of the active rows are >= 0."""
+    H, g, G, c = condense(qp)
+    lb, ub = qp['lb'].reshape(-1), qp['ub'].reshape(-1)
+    al, au = np.asarray(act_l, bool).reshape(-1), np.asarray(act_u, bool).reshape(-1)
+    U = np.zeros_like(g)
+    U[al], U[au] = lb[al], ub[au]
+    fixed = al | au
+    free = ~fixed
+    if free.any():
+        U[free] = np.linalg.solve(H[np.ix_(free, free)],
+                                  -(g[free] + H[np.ix_(free, fixed)] @ U[fixed]))
+    grad = H @ U + g                      # = lam_l - lam_u on the active rows, 0 on the free ones
+    N = qp['A'].shape[0]
+    dx = np.einsum('kij,j->ki', G, U) + c
+    return (dx, U.reshape(N, NU), np.where(al, grad, 0.0).reshape(N, NU),
+            np.where(au, -grad, 0.0).reshape(N, NU))
 
 
 def kkt_residuals(qp, dx, du, lam_l, lam_u):

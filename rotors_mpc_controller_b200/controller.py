@@ -296,6 +296,10 @@ class BatchedPositionNMPC:
             raise ValueError('mask must have one entry per problem')
         _abi.check(_abi.lib().nmpc_invalidate(self._h.ptr, _abi.ptr(m)), 'nmpc_invalidate')
 
+    def debug_poison(self, on: bool = True) -> None:
+        """NaN-fill workspace and shared tile before use (see nmpc_debug_poison)."""
+        _abi.check(_abi.lib().nmpc_debug_poison(self._h.ptr, int(bool(on))), 'nmpc_debug_poison')
+
     def reset_last_command(self) -> None:
         _abi.check(_abi.lib().nmpc_reset_last_command(self._h.ptr), 'nmpc_reset_last_command')
 

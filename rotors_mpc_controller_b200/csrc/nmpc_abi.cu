@@ -181,6 +181,7 @@ struct nmpc_handle {
   int batch, device, sm_count, grid, nslots, launches;
   int fixed_n;      // 1: the N = 20 instantiation of the solve kernel runs
   int stage_bytes;  // bytes of inputs the solve kernel stages by TMA per problem (0: direct loads)
+  int poison;       // debug: NaN-fill workspace (per launch) and shared tile (per problem)
   WsLayout L;
   size_t ws_bytes;
   void* ws;
@@ -488,10 +489,12 @@ static int launch_solve(nmpc_handle* h, const double* x0, const double* yref, co
   A.ws = reinterpret_cast<T*>(h->ws);
   // bulk copies need 16-byte aligned sources: the caller's yref may not be (then direct loads)
   A.stage = (h->stage_bytes > 0 && (reinterpret_cast<uintptr_t>(yref) & 15) == 0) ? 1 : 0;
+  A.poison = h->poison;
   const size_t smem = solve_smem_bytes<T>(h);
   // one workspace per handle: a solve on another stream than the previous one queues behind it
   CK(cudaStreamWaitEvent(st, h->ev_last, 0));
   CK(cudaMemsetAsync(h->counter, 0, sizeof(int), st));
+  if (h->poison) CK(cudaMemsetAsync(h->ws, 0xff, h->ws_bytes, st));  // all-ones = NaN in FP64 / FP32
   nmpc_solve_kernel<T, NS, NF>
       <<<h->grid, WARPS * 32, smem, st>>>(A, h->L, h->counter);
   h->launches++;
@@ -796,6 +799,12 @@ int nmpc_fp64_peak(int32_t device, double* tflops) {
   cudaEventDestroy(e1);
   cudaFree(buf);
   *tflops = best;
+  return NMPC_OK;
+}
+
+int nmpc_debug_poison(nmpc_handle_t* h, int32_t on) {
+  if (!h) return NMPC_E_INVALID;
+  h->poison = on ? 1 : 0;
   return NMPC_OK;
 }
 

@@ -631,6 +631,9 @@ struct SolveArgs {
   int* sqp_iters;
   T* ws;                 // nslots * layout.total
   int stage;             // 1: inputs staged by TMA bulk copies (make_stage_layout), 0: direct loads
+  int poison;            // debug (nmpc_debug_poison): the shared tile is filled with NaN before every
+                         // problem (and the host fills the workspace with NaN before every launch):
+                         // any read of memory the problem did not write itself changes the results
 };
 
 template <typename T>
@@ -711,6 +714,12 @@ __device__ __forceinline__ void solve_one(const SolveArgs<T>& A, const WsLayout&
   const double* yref_e = A.yref_e + (size_t)prob * NX;
   double* xtraj = A.xtraj + (size_t)prob * nxv;
   double* utraj = A.utraj + (size_t)prob * nuv;
+  if (A.poison) {  // debug: nothing of the previous problem may be read (see SolveArgs::poison)
+    const T nan = (T)__int_as_float(0x7fc00000);
+    _Pragma("unroll 1") for (int i = lane; i < SmemLayout::total; i += 32)
+      if (i < SmemLayout::bar || i >= SmemLayout::bar + 4) sm[i] = nan;
+    __syncwarp();
+  }
   // inputs -> workspace (TMA-staged when possible) + the gradients of the first SQP iteration
   load_inputs<T, NF>(A, L, ws, sm, prob, lane);
 

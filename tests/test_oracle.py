@@ -133,20 +133,38 @@ def _qp_cases(O, cfg, rng, n, cold):
 
 @pytest.mark.parametrize('cold', [True, False])
 def test_qp_against_independent_active_set(O, cfg, cold):
-    """Riccati IPM vs BVLS on the condensed QP: two unrelated algorithms, same optimum."""
+    """Riccati IPM vs two solvers that share no code with it, on 24 bound-active QPs.
+    (1) BVLS on the condensed QP finds the optimal active set on its own; it must be the set the
+        interior point reports (multiplier > slack).
+    (2) For that set the equality-constrained KKT system is solved DENSELY (numpy solve): the
+        exact vertex.  The interior point stops at complementarity mu <= ipm_tol, i.e. at distance
+        ~mu / lambda* from the vertex: <= 5e-10 at the default ipm_tol = 1e-14 (measured worst case
+        2.5e-10), <= 1e-11 at ipm_tol = 1e-18 (worst 4.4e-12); multipliers agree likewise and are
+        non-negative on every active row, the vertex is primal feasible."""
     from oracle import qp_check as Q
     rng = np.random.default_rng(4 + cold)
     nact_total = 0
     for qp in _qp_cases(O, cfg, rng, 12, cold):
+        for tol, bound in ((1e-14, 5e-10), (1e-18, 1e-11)):
+            s = O.qp_solve(qp, tol=tol)
+            assert s['status'] == 0 and s['iters'] <= 30
+            act_l = s['lam_l'] > (s['du'] - qp['lb'])
+            act_u = s['lam_u'] > (qp['ub'] - s['du'])
+            dx, du, ll, lu = Q.active_set_kkt(qp, act_l, act_u)
+            assert np.max(np.abs(du - s['du'])) <= bound
+            assert np.max(np.abs(dx - s['dx'])) <= bound
+            assert np.max(np.abs(ll - s['lam_l'])) <= bound and np.max(np.abs(lu - s['lam_u'])) <= bound
+            assert ll[act_l].min(initial=1.0) > 0 and lu[act_u].min(initial=1.0) > 0   # dual feasible
+            assert np.all(du >= qp['lb'] - 1e-15) and np.all(du <= qp['ub'] + 1e-15)    # primal feasible
+        # the active set found independently by BVLS is the same one
+        dxb, dub = Q.condensed_active_set(qp)
+        assert np.array_equal(dub <= qp['lb'] + 1e-9, act_l) and np.array_equal(dub >= qp['ub'] - 1e-9, act_u)
+        assert np.max(np.abs(dub - du)) < 1e-10
         s = O.qp_solve(qp)
-        assert s['status'] == 0 and s['iters'] <= 30
-        dx, du = Q.condensed_active_set(qp)
-        assert np.max(np.abs(du - s['du'])) < 2e-7   # weakly active rows limit both to ~sqrt(mu)
-        assert np.max(np.abs(dx - s['dx'])) < 2e-7
         k = Q.kkt_residuals(qp, s['dx'], s['du'], s['lam_l'], s['lam_u'])
         assert k['dyn'] < 1e-11 and k['stat'] < 1e-9 and k['comp'] < 1e-11 and k['feas'] < 1e-12
-        nact_total += int(np.sum((du <= qp['lb'] + 1e-9) | (du >= qp['ub'] - 1e-9)))
-    assert nact_total > 20
+        nact_total += int(act_l.sum() + act_u.sum())
+    assert nact_total > 100
 
 
 def test_unconstrained_qp_is_one_factorisation(O, cfg):
