@@ -63,6 +63,13 @@ typedef struct nmpc_config {
   int32_t ipm_warm_start;  /* 1: inside one solve with max_sqp_iter > 1, QPs after the first start the
                               interior point from the previous QP's slacks / multipliers (see
                               NMPC_WARM_*); 0: every QP starts cold.  RTI solves are not affected */
+  int32_t active_set_shortcut; /* 1: inside one solve with max_sqp_iter > 1, a QP first tries the
+                              previous QP's active set: the equality-constrained problem with those
+                              inputs fixed on their bounds is solved exactly in ONE factorisation and
+                              accepted iff it is primal feasible with non-negative multipliers (then
+                              it IS the QP solution); otherwise the interior point runs as before.
+                              0: interior point only.  RTI solves are not affected */
+  int32_t reserved0;       /* keeps the doubles 8-byte aligned; must be 0 */
   double dt;
   double W[17];            /* stage weights [p(3) v(3) q(4) w(3) u(4)] (controller.py:234-240) */
   double We[13];           /* terminal weights (controller.py:241) */

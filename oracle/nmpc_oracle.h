@@ -64,6 +64,8 @@ typedef struct {
   int nan_status;     /* status reported when NaNs appear (4 = QP failure, or 1) */
   int ipm_warm;       /* 1: QPs after the first of an SQP run (max_sqp_iter > 1) warm-start the
                          interior point from the previous QP's (t, lam), see ORC_WARM_* */
+  int as_shortcut;    /* 1: QPs after the first of an SQP run first try the previous QP's active set
+                         (orc_qp_solve_active_set, one factorisation) before the interior point */
   int keep_state_box; /* 1: the +-state_box rows on all 13 states at stages 1..N-1
                          (controller.py:257-261) are real inequality rows of the QP, as in the
                          reference's HPIPM problem.  ORACLE-ONLY sensitivity flag (default 0): the
@@ -129,6 +131,11 @@ int orc_qp_solve(const orc_qp *qp, int iter_max, double tol, double *dx, double 
 int orc_qp_solve_warm(const orc_qp *qp, int iter_max, double tol, double *dx, double *du,
                       double *lam_l, double *lam_u, double *t_l_io, double *t_u_io, double warm_eps,
                       int *ipm_converged, int *iters);
+
+/* Exact solve for a given active set (act[N*4]: 0 free, 1 lower, 2 upper) in one factorisation;
+ * returns 0 when the point is the QP solution (primal feasible, multipliers >= 0), else 1. */
+int orc_qp_solve_active_set(const orc_qp *qp, const unsigned char *act, double *dx, double *du,
+                            double *lam_l, double *lam_u);
 
 /* One PositionNMPC.solve() (controller.py:385-463) for a single problem.
  * xtraj/utraj/valid are the warm-start store (in/out).  x0 must already hold the

@@ -301,6 +301,180 @@ static void riccati_delta_solve(const orc_qp *qp, const double *dr, const double
   }
 }
 
+/* ------------------------------------------------------- active-set shortcut */
+/* Exact solve of the QP for a GIVEN active set (act[i]: 0 free, 1 on the lower, 2 on the upper
+ * bound) in ONE Riccati factorisation: the active inputs are eliminated stage by stage
+ * (du_i = bound, their row / column of Quu replaced by the identity, their coupling moved to the
+ * gradients), the forward roll-out gives (dx, du), a costate sweep gives the multipliers
+ *     s = R du + r + B' pi_{k+1} = lam_l - lam_u .
+ * The point is THE solution of the QP (strictly convex) iff it is primal feasible on the free rows
+ * and the multipliers of the active rows are non-negative; then 0 is returned, otherwise 1 and the
+ * caller falls back to the interior point.  Used between the QPs of one SQP run once the active set
+ * has settled (orc_solve): same solutions, one factorisation instead of several. */
+int orc_qp_solve_active_set(const orc_qp *qp, const unsigned char *act, double *dx, double *du,
+                            double *lam_l, double *lam_u) {
+  const int N = qp->N;
+  const int nb = N * NU;
+  double *Ks = (double *)malloc(sizeof(double) * (size_t)N * NU * NX);
+  double *kffs = (double *)malloc(sizeof(double) * (size_t)N * NU);
+  int bad = 0;
+  double P[NX * NX] = {0}, p[NX];
+  for (int i = 0; i < NX; i++) {
+    P[i * NX + i] = qp->Q[N * NX + i];
+    p[i] = qp->q[N * NX + i];
+  }
+  for (int k = N - 1; k >= 0 && !bad; k--) {
+    const double *A = qp->A + (size_t)k * NX * NX;
+    const double *B = qp->B + (size_t)k * NX * NU;
+    const double *b = qp->b + (size_t)k * NX;
+    double PA[NX * NX], PB[NX * NU], w[NX];
+    for (int i = 0; i < NX; i++) {
+      for (int j = 0; j < NX; j++) {
+        double s = 0;
+        for (int l = 0; l < NX; l++) s += P[i * NX + l] * A[l * NX + j];
+        PA[i * NX + j] = s;
+      }
+      for (int j = 0; j < NU; j++) {
+        double s = 0;
+        for (int l = 0; l < NX; l++) s += P[i * NX + l] * B[l * NU + j];
+        PB[i * NU + j] = s;
+      }
+      double s = p[i];
+      for (int l = 0; l < NX; l++) s += P[i * NX + l] * b[l];
+      w[i] = s;
+    }
+    double Quu[16], Qux[NU * NX], Qxx[NX * NX], gu[NU], gx[NX];
+    for (int i = 0; i < NU; i++) {
+      for (int j = 0; j < NU; j++) {
+        double s = (i == j) ? qp->R[k * NU + i] : 0.0;
+        for (int l = 0; l < NX; l++) s += B[l * NU + i] * PB[l * NU + j];
+        Quu[i * 4 + j] = s;
+      }
+      for (int j = 0; j < NX; j++) {
+        double s = 0;
+        for (int l = 0; l < NX; l++) s += B[l * NU + i] * PA[l * NX + j];
+        Qux[i * NX + j] = s;
+      }
+      double s = qp->r[k * NU + i];
+      for (int l = 0; l < NX; l++) s += B[l * NU + i] * w[l];
+      gu[i] = s;
+    }
+    for (int i = 0; i < NX; i++) {
+      for (int j = 0; j < NX; j++) {
+        double s = (i == j) ? qp->Q[k * NX + i] : 0.0;
+        for (int l = 0; l < NX; l++) s += A[l * NX + i] * PA[l * NX + j];
+        Qxx[i * NX + j] = s;
+      }
+      double s = qp->q[k * NX + i];
+      for (int l = 0; l < NX; l++) s += A[l * NX + i] * w[l];
+      gx[i] = s;
+    }
+    /* eliminate the active inputs: du_i = d_i */
+    for (int i = 0; i < NU; i++) {
+      const int a = act[k * NU + i];
+      if (!a) continue;
+      const double d = (a == 1) ? qp->lb[k * NU + i] : qp->ub[k * NU + i];
+      for (int j = 0; j < NU; j++)
+        if (j != i && !act[k * NU + j]) gu[j] += Quu[j * 4 + i] * d;
+      for (int j = 0; j < NX; j++) gx[j] += Qux[i * NX + j] * d;
+    }
+    for (int i = 0; i < NU; i++) {
+      if (!act[k * NU + i]) continue;
+      const int a = act[k * NU + i];
+      const double d = (a == 1) ? qp->lb[k * NU + i] : qp->ub[k * NU + i];
+      for (int j = 0; j < NU; j++) Quu[i * 4 + j] = Quu[j * 4 + i] = 0.0;
+      Quu[i * 4 + i] = 1.0;
+      for (int j = 0; j < NX; j++) Qux[i * NX + j] = 0.0;
+      gu[i] = -d;
+    }
+    double Qi[16];
+    if (chol4_inv(Quu, Qi)) {
+      bad = 1;
+      break;
+    }
+    double *K = Ks + (size_t)k * NU * NX;
+    double *kff = kffs + (size_t)k * NU;
+    for (int i = 0; i < NU; i++) {
+      for (int j = 0; j < NX; j++) {
+        double s = 0;
+        for (int l = 0; l < NU; l++) s -= Qi[i * 4 + l] * Qux[l * NX + j];
+        K[i * NX + j] = s;
+      }
+      double s = 0;
+      for (int l = 0; l < NU; l++) s -= Qi[i * 4 + l] * gu[l];
+      kff[i] = s;
+    }
+    for (int i = 0; i < NX; i++) {
+      for (int j = 0; j < NX; j++) {
+        double s = Qxx[i * NX + j];
+        for (int l = 0; l < NU; l++) s += Qux[l * NX + i] * K[l * NX + j];
+        P[i * NX + j] = s;
+      }
+      double s = gx[i];
+      for (int l = 0; l < NU; l++) s += Qux[l * NX + i] * kff[l];
+      p[i] = s;
+    }
+    for (int i = 0; i < NX; i++)
+      for (int j = i + 1; j < NX; j++) {
+        const double m = 0.5 * (P[i * NX + j] + P[j * NX + i]);
+        P[i * NX + j] = P[j * NX + i] = m;
+      }
+  }
+  if (!bad) {
+    memset(dx, 0, sizeof(double) * NX);
+    for (int k = 0; k < N; k++) {
+      const double *A = qp->A + (size_t)k * NX * NX;
+      const double *B = qp->B + (size_t)k * NX * NU;
+      const double *K = Ks + (size_t)k * NU * NX;
+      const double *x = dx + (size_t)k * NX;
+      double *u = du + (size_t)k * NU;
+      double *xn = dx + (size_t)(k + 1) * NX;
+      for (int i = 0; i < NU; i++) {
+        double s = kffs[k * NU + i];
+        for (int j = 0; j < NX; j++) s += K[i * NX + j] * x[j];
+        const int a = act[k * NU + i];
+        u[i] = a ? ((a == 1) ? qp->lb[k * NU + i] : qp->ub[k * NU + i]) : s; /* exactly on the bound */
+      }
+      for (int i = 0; i < NX; i++) {
+        double s = qp->b[k * NX + i];
+        for (int j = 0; j < NX; j++) s += A[i * NX + j] * x[j];
+        for (int j = 0; j < NU; j++) s += B[i * NU + j] * u[j];
+        xn[i] = s;
+      }
+    }
+    /* costate sweep: multipliers of the active rows, primal feasibility of the free ones */
+    double pi[NX];
+    for (int i = 0; i < NX; i++) pi[i] = qp->Q[N * NX + i] * dx[N * NX + i] + qp->q[N * NX + i];
+    for (int k = N - 1; k >= 0; k--) {
+      const double *A = qp->A + (size_t)k * NX * NX;
+      const double *B = qp->B + (size_t)k * NX * NU;
+      for (int i = 0; i < NU; i++) {
+        double s = qp->R[k * NU + i] * du[k * NU + i] + qp->r[k * NU + i];
+        for (int l = 0; l < NX; l++) s += B[l * NU + i] * pi[l];
+        const int a = act[k * NU + i];
+        lam_l[k * NU + i] = (a == 1) ? s : 0.0;
+        lam_u[k * NU + i] = (a == 2) ? -s : 0.0;
+        if (a == 1 && !(s >= 0.0)) bad = 1;
+        if (a == 2 && !(-s >= 0.0)) bad = 1;
+        if (!a && !(du[k * NU + i] >= qp->lb[k * NU + i] && du[k * NU + i] <= qp->ub[k * NU + i]))
+          bad = 1;
+      }
+      double pn[NX];
+      for (int i = 0; i < NX; i++) {
+        double s = qp->Q[k * NX + i] * dx[k * NX + i] + qp->q[k * NX + i];
+        for (int l = 0; l < NX; l++) s += A[l * NX + i] * pi[l];
+        pn[i] = s;
+      }
+      memcpy(pi, pn, sizeof(pn));
+    }
+    for (int i = 0; i < nb; i++)
+      if (!(du[i] == du[i])) bad = 1;
+  }
+  free(Ks);
+  free(kffs);
+  return bad;
+}
+
 /* ------------------------------------------------------- interior point */
 /* Weight of Mehrotra's second-order term.  With a short affine step the full term
  * dt_aff*dlam_aff over-corrects and the iteration can fall into a 2-cycle (seen on warm

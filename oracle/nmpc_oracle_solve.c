@@ -13,6 +13,9 @@
 #define NU ORC_NU
 #define NZ ORC_NZ
 
+/* diagnostics (not thread-safe, per process): active-set shortcut attempts */
+long orc_as_accepted = 0, orc_as_rejected = 0;
+
 static int has_nan(const double *v, int n) {
   for (int i = 0; i < n; i++)
     if (!(v[i] == v[i]) || isinf(v[i])) return 1;
@@ -32,6 +35,10 @@ int orc_solve(const orc_config *c, const double *x0, const double *yref, const d
   double *lu = (double *)malloc(sizeof(double) * (size_t)N * NU);
   double *tl = (double *)calloc((size_t)N * NU, sizeof(double));
   double *tu = (double *)calloc((size_t)N * NU, sizeof(double));
+  double *ll2 = (double *)malloc(sizeof(double) * (size_t)N * NU);
+  double *lu2 = (double *)malloc(sizeof(double) * (size_t)N * NU);
+  unsigned char *act = (unsigned char *)malloc((size_t)N * NU);
+  int n_as_ok = 0, n_as_fail = 0;
   orc_qp *qp = orc_qp_alloc(N);
 
   if (*valid) { /* controller.py:419-424 : previous solution, NOT shifted; stage 0 x <- x0 (:416) */
@@ -54,8 +61,34 @@ int orc_solve(const orc_config *c, const double *x0, const double *yref, const d
     double weps = 0.0;
     if (c->ipm_warm && !c->keep_state_box && have_ipm && prev_step <= ORC_WARM_STEP_MAX)
       weps = fmin(fmax(ORC_WARM_KAPPA * prev_step, ORC_WARM_EPS_MIN), ORC_WARM_EPS_MAX);
-    const int qs = orc_qp_solve_warm(qp, c->qp_iter_max, c->ipm_tol, dx, du, ll, lu, tl, tu, weps,
-                                     &have_ipm, &qi);
+    int qs = -1;
+    /* Active-set shortcut: the previous QP of this solve left a converged (t, lam); if its active
+     * set is still the right one this QP is solved exactly by one factorisation. */
+    if (c->as_shortcut && !c->keep_state_box && have_ipm) {
+      int nact = 0;
+      for (int i = 0; i < N * NU; i++) {
+        act[i] = (ll[i] > tl[i]) ? 1 : ((lu[i] > tu[i]) ? 2 : 0);
+        nact += act[i] != 0;
+      }
+      if (nact > 0) {
+        tot_qp++;
+        if (orc_qp_solve_active_set(qp, act, dx, du, ll2, lu2) == 0) {
+          qs = ORC_SUCCESS;
+          memcpy(ll, ll2, sizeof(double) * (size_t)N * NU);
+          memcpy(lu, lu2, sizeof(double) * (size_t)N * NU);
+          for (int i = 0; i < N * NU; i++) { /* slacks of the accepted point (0 on active rows) */
+            tl[i] = (act[i] == 1) ? 0.0 : du[i] - qp->lb[i];
+            tu[i] = (act[i] == 2) ? 0.0 : qp->ub[i] - du[i];
+          }
+          n_as_ok++;
+        } else {
+          n_as_fail++;
+        }
+      }
+    }
+    if (qs < 0)
+      qs = orc_qp_solve_warm(qp, c->qp_iter_max, c->ipm_tol, dx, du, ll, lu, tl, tu, weps, &have_ipm,
+                             &qi);
     tot_qp += qi;
     nsqp++;
     /* UPSTREAM acados SQP_RTI: a QP that only hit its iteration cap is tolerated. */
@@ -105,6 +138,11 @@ int orc_solve(const orc_config *c, const double *x0, const double *yref, const d
   free(lu);
   free(tl);
   free(tu);
+  free(ll2);
+  free(lu2);
+  free(act);
+  orc_as_accepted += n_as_ok;
+  orc_as_rejected += n_as_fail;
   return status;
 }
 

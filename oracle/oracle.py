@@ -33,7 +33,8 @@ class OrcConfig(C.Structure):
         ('w_max', C.c_double), ('integ_ns', C.c_int), ('integ_steps', C.c_int),
         ('cost_scale_dt', C.c_int), ('lm_scaled_by_dt', C.c_int), ('max_sqp_iter', C.c_int),
         ('sqp_tol', C.c_double), ('ipm_tol', C.c_double), ('nan_status', C.c_int),
-        ('ipm_warm', C.c_int), ('keep_state_box', C.c_int), ('state_box', C.c_double),
+        ('ipm_warm', C.c_int), ('as_shortcut', C.c_int), ('keep_state_box', C.c_int),
+        ('state_box', C.c_double),
     ]
 
 
@@ -128,6 +129,7 @@ def config_from_params(params: Dict[str, Dict[str, object]], **flags) -> OrcConf
     c.ipm_tol = float(flags.get('ipm_tol', 1e-14))
     c.nan_status = int(flags.get('nan_status', 4))
     c.ipm_warm = int(bool(flags.get('ipm_warm', s.get('ipm_warm_start', True))))
+    c.as_shortcut = int(bool(flags.get('as_shortcut', s.get('active_set_shortcut', True))))
     c.keep_state_box = int(flags.get('keep_state_box', 0))   # controller.py:257-261 (oracle-only)
     c.state_box = float(flags.get('state_box', 1.0e6))
     return c

@@ -134,6 +134,8 @@ def abi_config(cp: ControllerParams, solver_cfg: Dict[str, object]) -> _abi.Nmpc
     c.max_sqp_iter = int(solver_cfg.get('max_sqp_iter', 1))     # SQP_RTI (nlp_solver_type unset)
     c.nan_status = int(solver_cfg.get('nan_status', 4))
     c.ipm_warm_start = int(bool(solver_cfg.get('ipm_warm_start', True)))
+    c.active_set_shortcut = int(bool(solver_cfg.get('active_set_shortcut', True)))
+    c.reserved0 = 0
     prec = str(solver_cfg.get('precision', 'f64')).lower()
     if prec not in ('f64', 'f32'):
         raise ValueError('precision must be "f64" or "f32"')

@@ -138,6 +138,7 @@ DevCfg<T> make_devcfg(const nmpc_config_t& c) {
   d.max_sqp_iter = c.max_sqp_iter;
   d.nan_status = c.nan_status;
   d.ipm_warm = c.ipm_warm_start != 0;
+  d.as_shortcut = c.active_set_shortcut != 0;
   d.dt = (T)c.dt;
   d.h = (T)(c.dt / (double)c.integ_steps);
   const double sc = c.cost_scale_dt ? c.dt : 1.0;
@@ -807,6 +808,19 @@ int nmpc_debug_poison(nmpc_handle_t* h, int32_t on) {
   h->poison = on ? 1 : 0;
   return NMPC_OK;
 }
+
+#ifdef NMPC_PROFILE
+// Instrumented build only (scripts/phase_profile.py): read and clear the per-phase cycle counters.
+int nmpc_debug_phase_cycles(double* out, int32_t n) {
+  unsigned long long v[PH_COUNT];
+  CK(cudaDeviceSynchronize());
+  CK(cudaMemcpyFromSymbol(v, g_phase_cycles, sizeof(v)));
+  for (int i = 0; i < n && i < PH_COUNT; i++) out[i] = (double)v[i];
+  memset(v, 0, sizeof(v));
+  CK(cudaMemcpyToSymbol(g_phase_cycles, v, sizeof(v)));
+  return NMPC_OK;
+}
+#endif
 
 int nmpc_batch(const nmpc_handle_t* h) { return h ? h->batch : NMPC_E_INVALID; }
 int nmpc_horizon(const nmpc_handle_t* h) { return h ? h->cfg.N : NMPC_E_INVALID; }

@@ -18,6 +18,7 @@ template <typename T>
 struct DevCfg {
   int N, qp_iter_max, integ_steps, max_sqp_iter, nan_status;
   bool ipm_warm;      // interior-point warm start between the QPs of one SQP run
+  bool as_shortcut;   // active-set shortcut between the QPs of one SQP run (see as_solve)
   T dt, h;            // shooting interval and integrator sub-step
   T Wq[NX], Wr[NU];   // scaled stage weights (sc * W)
   T Qd[NX], Rd[NU];   // stage Hessian diagonals incl. LM

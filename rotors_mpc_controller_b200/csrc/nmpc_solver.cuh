@@ -28,6 +28,24 @@ constexpr unsigned FULL = 0xffffffffu;
 
 enum : int { ST_SUCCESS = 0, ST_NAN = 1, ST_MAXITER = 2, ST_MINSTEP = 3, ST_QPFAIL = 4 };
 
+// Phase timers of the instrumented build (-DNMPC_PROFILE, scripts/phase_profile.py): cycles per
+// phase summed over all warps.  Compiled out of the product library.
+enum : int { PH_LOAD = 0, PH_LIN, PH_GRAD, PH_FACTOR, PH_FWD, PH_DELTA, PH_ELEM, PH_STEP, PH_EPI,
+             PH_TOTAL, PH_COUNT };
+#ifdef NMPC_PROFILE
+__device__ unsigned long long g_phase_cycles[PH_COUNT];
+#define PROF_T0() long long prof_t_ = clock64()
+#define PROF_ADD(ph_)                                                                   \
+  do {                                                                                  \
+    const long long now_ = clock64();                                                   \
+    if (lane == 0) atomicAdd(&g_phase_cycles[ph_], (unsigned long long)(now_ - prof_t_)); \
+    prof_t_ = now_;                                                                     \
+  } while (0)
+#else
+#define PROF_T0() do { } while (0)
+#define PROF_ADD(ph_) do { } while (0)
+#endif
+
 // Offsets (in elements of T) inside one workspace slot.
 struct WsLayout {
   int N;
@@ -333,6 +351,7 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
                                          T warm_eps, bool* ipm_conv, int* iters) {
   *ipm_conv = false;
   NMPC_FIXED(c)
+  PROF_T0();
   const int nb = N * NU;
   const int nxv = (N + 1) * NX;
   const T thr0 = T(0.1), mu0 = T(0.1);
@@ -370,13 +389,16 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
   __syncwarp();
   if (!skip0) {
     res0 = T(0);  // b and q are met exactly by the phase-0 point
-    const bool ok0 = factor_sweep<T, NF>(c, ws, L, sm, lane, T(1));
+    PROF_ADD(PH_ELEM);
+    const bool ok0 = factor_sweep<T, NF>(c, ws, L, sm, lane, T(1), false);
+    PROF_ADD(PH_FACTOR);
     it = 1;
     if (!ok0) {
       *iters = it;
       return ST_QPFAIL;
     }
     forward_sweep<T, NF>(c, ws, L, sm, lane, T(1), false, true, false, L.kff, L.dx, L.du);
+    PROF_ADD(PH_FWD);
   }
   // box check + interior-point start
   bool feas = !skip0;
@@ -408,6 +430,7 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
   }
   if (__all_sync(FULL, feas)) {
     *iters = it;
+    PROF_ADD(PH_ELEM);
     return ST_SUCCESS;
   }
   res0 = warp_max(res0);
@@ -468,7 +491,9 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
     }
     __syncwarp();
     const T rq = skip0 ? rho : T(0);
-    const bool ok = factor_sweep<T, NF>(c, ws, L, sm, lane, rq);
+    PROF_ADD(PH_ELEM);
+    const bool ok = factor_sweep<T, NF>(c, ws, L, sm, lane, rq, false);
+    PROF_ADD(PH_FACTOR);
     if (!ok) {
       // FP32 precision floor: once the complementarity is below 1e-6 a lost pivot means the
       // barrier Hessian can no longer be resolved in single precision -> keep the iterate
@@ -476,6 +501,7 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
       break;
     }
     forward_sweep<T, NF>(c, ws, L, sm, lane, rq, false, false, false, L.kff, L.dx, L.ua);   // wx = false: no state output
+    PROF_ADD(PH_FWD);
     // affine step length (division-free ratio test: the running minimum is kept as a fraction
     // an/ad and candidates are compared by cross-multiplication)
     T an = T(1), ad = T(1);
@@ -528,8 +554,11 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
     })
     __syncwarp();
     // corrector increment (vector-only re-solve), accumulated onto the predictor direction
+    PROF_ADD(PH_ELEM);
     delta_backward<T, NF>(c, ws, L, sm, lane);
+    PROF_ADD(PH_DELTA);
     forward_sweep<T, NF>(c, ws, L, sm, lane, T(0), true, false, false, L.kffd, L.dx, L.ua);
+    PROF_ADD(PH_FWD);
     T bn = T(2), bd = T(1);  // ratios >= 2 cannot bind: alpha = min(1, tau * ratio), tau >= 0.995
     bool fin = true;         // NaN anywhere must surface: comparisons drop NaNs, so test explicitly
     NMPC_ROWS({
@@ -605,10 +634,66 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
   // The state direction is only needed once: roll the linearised dynamics out for the final
   // input direction, dx_{k+1} = A_k dx_k + B_k du_k + b_k (instead of updating dx every iteration).
   __syncwarp();
+  PROF_ADD(PH_ELEM);
   forward_sweep<T, NF>(c, ws, L, sm, lane, T(1), false, true, true, L.kff, L.dx, L.du);
+  PROF_ADD(PH_FWD);
   *iters = it;
   *ipm_conv = (status == ST_SUCCESS);
   return status;
+}
+
+// ------------------------------------------------------------------ K2': active-set shortcut
+// Between the QPs of one SQP run the active set settles long before the iterate does.  When the
+// previous QP of this solve left a converged interior-point iterate (or an accepted shortcut), its
+// active set  { i : lam_i > t_i }  is tried first: the inputs of that set are fixed on their bounds
+// of the NEW QP, the remaining equality-constrained problem is solved exactly by one Riccati
+// factorisation with those inputs eliminated (factor_sweep asmode) + roll-out, and a costate sweep
+// delivers the multipliers.  The point is accepted iff it is primal feasible on the free rows and
+// dual feasible on the fixed ones -- then it IS the solution of the strictly convex QP, exact to
+// round-off, for one factorisation instead of the 3-6 of a warm interior point.  Otherwise nothing
+// is committed (t, lam of the previous QP are untouched) and the interior point runs as before.
+// Returns true when accepted; *tried = 1 when a factorisation was spent.
+template <typename T, int NF>
+__device__ __forceinline__ bool as_solve(const DevCfg<T>& c, T* __restrict__ ws,
+                                         const WsLayout& Lr, T* __restrict__ sm, int lane,
+                                         int* tried) {
+  NMPC_FIXED(c)
+  PROF_T0();
+  const int nb = N * NU;
+  const T nan = (T)__int_as_float(0x7fc00000);
+  *tried = 0;
+  bool any = false;
+  _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
+    const bool lo = ws[L.ll + i] > ws[L.tl + i];
+    const bool up = !lo && (ws[L.lu + i] > ws[L.tu + i]);
+    ws[L.dr + i] = lo ? ws[L.lb + i] : (up ? ws[L.ubd + i] : nan);   // fixed value (NaN: free)
+    ws[L.dtl + i] = lo ? T(1) : (up ? T(2) : T(0));                  // row code
+    ws[L.rt + i] = ws[L.r + i];                                       // plain input gradient
+    any = any || lo || up;
+  }
+  if (!__any_sync(FULL, any)) return false;  // nothing active: the phase-0 solve is the shortcut
+  __syncwarp();
+  *tried = 1;
+  PROF_ADD(PH_ELEM);
+  bool ok = factor_sweep<T, NF>(c, ws, L, sm, lane, T(1), true);
+  PROF_ADD(PH_FACTOR);
+  if (!ok) return false;
+  forward_sweep<T, NF>(c, ws, L, sm, lane, T(1), false, true, false, L.kff, L.dx, L.du);
+  PROF_ADD(PH_FWD);
+  ok = costate_check<T, NF>(c, ws, L, sm, lane);
+  PROF_ADD(PH_DELTA);
+  if (!ok) return false;
+  // accepted: slacks / multipliers of this point are the warm start and active set of the next QP
+  _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
+    const T code = ws[L.dtl + i], du = ws[L.du + i];
+    ws[L.tl + i] = code == T(1) ? T(0) : du - ws[L.lb + i];
+    ws[L.tu + i] = code == T(2) ? T(0) : ws[L.ubd + i] - du;
+    ws[L.ll + i] = ws[L.dll + i];
+    ws[L.lu + i] = ws[L.dlu + i];
+  }
+  __syncwarp();
+  PROF_ADD(PH_ELEM);
+  return true;
 }
 
 // ------------------------------------------------------------------ whole solve (K1+K2+K3)
@@ -720,8 +805,13 @@ __device__ __forceinline__ void solve_one(const SolveArgs<T>& A, const WsLayout&
       if (i < SmemLayout::bar || i >= SmemLayout::bar + 4) sm[i] = nan;
     __syncwarp();
   }
+  PROF_T0();
+#ifdef NMPC_PROFILE
+  const long long prof_start_ = prof_t_;
+#endif
   // inputs -> workspace (TMA-staged when possible) + the gradients of the first SQP iteration
   load_inputs<T, NF>(A, L, ws, sm, prob, lane);
+  PROF_ADD(PH_LOAD);
 
   int status = ST_SUCCESS;
   int tot_qp = 0, nsqp = 0;
@@ -733,13 +823,24 @@ __device__ __forceinline__ void solve_one(const SolveArgs<T>& A, const WsLayout&
   const int max_sqp = c.max_sqp_iter < 1 ? 1 : c.max_sqp_iter;
   while (nsqp < max_sqp) {
     linearize<T, NS, NF>(c, ws, L, sm, lane);
+    PROF_ADD(PH_LIN);
     if (nsqp > 0) gradients<T, NF>(c, ws, L, yref, yref_e, lane);  // first iteration: done by load_inputs
     __syncwarp();
+    PROF_ADD(PH_GRAD);
     int qi = 0;
     T weps = T(0);
     if (c.ipm_warm && have_ipm && prev_step <= T(NMPC_WARM_STEP_MAX))
       weps = fmin(fmax(T(NMPC_WARM_KAPPA) * prev_step, eps_min), T(NMPC_WARM_EPS_MAX));
-    const int qs = ipm_solve<T, NF>(c, ws, L, sm, lane, weps, &have_ipm, &qi);
+    int qs = -1;
+    if (c.as_shortcut && have_ipm) {
+      int tried = 0;
+      if (as_solve<T, NF>(c, ws, L, sm, lane, &tried)) qs = ST_SUCCESS;
+      tot_qp += tried;
+    }
+    if (qs < 0) qs = ipm_solve<T, NF>(c, ws, L, sm, lane, weps, &have_ipm, &qi);
+#ifdef NMPC_PROFILE
+    prof_t_ = clock64();  // ipm_solve accounted for its own phases
+#endif
     tot_qp += qi;
     nsqp++;
     // acados SQP_RTI tolerates a QP that only hit its iteration cap
@@ -770,6 +871,7 @@ __device__ __forceinline__ void solve_one(const SolveArgs<T>& A, const WsLayout&
       break;
     }
     step = warp_max(step);
+    PROF_ADD(PH_STEP);
     prev_step = step;
     if (step <= c.sqp_tol) {
       converged = true;
@@ -803,6 +905,10 @@ __device__ __forceinline__ void solve_one(const SolveArgs<T>& A, const WsLayout&
     if (A.sqp_iters) A.sqp_iters[prob] = nsqp;
   }
   __syncwarp();
+  PROF_ADD(PH_EPI);
+#ifdef NMPC_PROFILE
+  if (lane == 0) atomicAdd(&g_phase_cycles[PH_TOTAL], (unsigned long long)(clock64() - prof_start_));
+#endif
 }
 
 }  // namespace nmpc

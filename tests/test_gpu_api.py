@@ -276,7 +276,8 @@ def test_sqp_ipm_warm_start_is_a_pure_speed_up(params, O):
     out = {}
     for warm in (False, True):
         p = copy.deepcopy(params)
-        p['solver'].update(max_sqp_iter=50, sqp_tol=1e-8, ipm_warm_start=warm)
+        p['solver'].update(max_sqp_iter=50, sqp_tol=1e-8, ipm_warm_start=warm,
+                           active_set_shortcut=False)     # isolate the interior-point warm start
         ctl = BatchedPositionNMPC(p, batch=B)
         if not warm:
             yref, yref_e = setpoint_refs(np.random.default_rng(22), x0, 20, ctl.hover_thrust)
@@ -296,6 +297,44 @@ def test_sqp_ipm_warm_start_is_a_pure_speed_up(params, O):
     assert out[True][2].sum() < 0.75 * out[False][2].sum()
     assert out[True][2].max() < 0.75 * out[False][2].max()
     assert np.mean(out[True][3] == out[False][3]) > 0.95      # same number of SQP iterations
+
+
+@pytest.mark.parametrize('kind', ['cfg2', 'aggressive'])
+def test_active_set_shortcut_is_a_pure_speed_up(params, O, kind):
+    """solver.active_set_shortcut (default on): inside one SQP run a QP first tries the previous
+    QP's active set -- an exact equality-constrained solve in ONE factorisation, accepted only if it
+    is primal and dual feasible (then it is the unique QP solution).  Same statuses, same SQP
+    iteration counts, converged u0 equal to the interior-point-only run within the SQP tolerance,
+    far fewer factorisations; the oracle with the same flag takes the same path."""
+    from rotors_mpc_controller_b200 import BatchedPositionNMPC
+    B = 384
+    out = {}
+    for on in (False, True):
+        p = copy.deepcopy(params)
+        p['solver'].update(max_sqp_iter=50, sqp_tol=1e-8, active_set_shortcut=on)
+        ctl = BatchedPositionNMPC(p, batch=B)
+        rng = np.random.default_rng(31)
+        if kind == 'cfg2':
+            x0 = random_states(rng, B)
+            yref, yref_e = setpoint_refs(rng, x0, 20, ctl.hover_thrust)
+        else:
+            x0, yref, yref_e = aggressive(rng, B, 20, ctl.hover_thrust)
+        u0, st = ctl.solve(x0, yref, yref_e)
+        s = ctl.stats()
+        ob = O.OracleBatch(O.config_from_params(p, max_sqp_iter=50, sqp_tol=1e-8), B)
+        ur, sr, _, _ = ob.solve(x0, yref, yref_e)
+        assert np.array_equal(st, sr)
+        ok = st == 0
+        assert np.max(np.abs(u0 - ur)[ok]) < 1e-7
+        assert np.mean(s['qp_iters'] == ob.qp_iters) > 0.97    # same path up to rounding ties
+        out[on] = (u0.copy(), st.copy(), s['qp_iters'].copy(), s['sqp_iters'].copy())
+        ctl.close()
+    assert np.array_equal(out[True][1], out[False][1])
+    ok = out[True][1] == 0
+    assert ok.mean() > (0.99 if kind == 'cfg2' else 0.3)
+    assert np.max(np.abs(out[True][0] - out[False][0])[ok]) < 1e-7
+    assert np.mean(out[True][3][ok] == out[False][3][ok]) > 0.95    # same number of SQP iterations
+    assert out[True][2][ok].sum() < (0.7 if kind == 'cfg2' else 0.9) * out[False][2][ok].sum()
 
 
 def test_fp32_sqp_with_warm_start(params):
