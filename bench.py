@@ -104,7 +104,10 @@ def run_reference(args):
         'unit': 'solves/s', 'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup,
         'ms_per_step': 1e3 * sum(times) / len(times), 'higher_is_better': True,
         'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
-        'config': workload_config(args.gpus),
+        'config': {**workload_config(args.gpus), 'batch_per_gpu': None, 'global_batch': n,
+                   'parallelism': f'one process per host core x{cores} (rank 0 only), no GPU',
+                   'l2': 'n/a (CPU arm)',
+                   'note': f'each step is a bounded sample of the workload: {n} problems'},
         'cpu_baseline': {'value': value, 'unit': 'solves/s', 'cores': cores, 'kind': 'port',
                          'sample': sample},
         'e2e': {'value': value, 'unit': 'solves/s', 'h2d_bytes_per_step': 0,
@@ -117,11 +120,14 @@ def run_reference(args):
 
 
 def workload_config(gpus):
+    par = (f'batch-sharded x{gpus}; per step an NCCL all-gather of (u0[4], status) per problem '
+           f'(40 B) on a side stream, overlapped with the next step' if gpus > 1
+           else 'single GPU (batch-sharded x1, nothing to gather)')
     return {'workload': 'configs[1]: batch 4096 hummingbirds per GPU, randomised states around '
                         'hover, random set-point steps, N=20, dt=0.05, cold start, SQP to '
                         'convergence (step<=1e-8, cap 50), ERK midpoint x2, u-box [0.0214,6.003] N',
             'batch_per_gpu': BATCH, 'horizon': HORIZON, 'global_batch': BATCH * gpus,
-            'parallelism': f'batch-sharded x{gpus}, no data-path collective',
+            'parallelism': par,
             'l2': 'flushed between timed steps (256 MiB write, outside the event pair)'}
 
 
@@ -168,6 +174,71 @@ class ClockSampler:
                 'samples': len(sm)}
 
 
+# ------------------------------------------------------------------ result gather (N > 1)
+class Gather:
+    """Per-step NCCL all-gather of (u0[B,4], status[B]) -- 40 B per problem -- on a side stream.
+    launch() is asynchronous: it orders itself behind the solve (event / stream), packs the two
+    outputs into one [B,5] tensor and all-gathers it; the next step's solve overlaps it."""
+
+    def __init__(self, ctl, dev, world):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist, self.dev, self.world = torch, dist, dev, world
+        self.side = torch.cuda.Stream(dev)
+        B = ctl.batch
+        self.pack = torch.zeros((B, 5), dtype=torch.float64, device=dev)
+        self.out = torch.empty((world * B, 5), dtype=torch.float64, device=dev)
+        self.events, self.launches, self.ctl = [], 0, ctl
+        self.last_local = None
+
+    def handle_outputs(self):
+        """Device-resident (u0, status) of the last nmpc_solve_host call (zero-copy views)."""
+        import ctypes as C
+        from rotors_mpc_controller_b200 import _abi
+        from rotors_mpc_controller_b200.closed_loop import _DeviceArray
+        B = self.ctl.batch
+        ptrs = [C.c_void_p() for _ in range(4)]
+        _abi.check(_abi.lib().nmpc_last_outputs(self.ctl._h.ptr, *[C.byref(p) for p in ptrs]),
+                   'nmpc_last_outputs')
+        u0 = self.torch.as_tensor(_DeviceArray(ptrs[0].value, (B, 4), '<f8'), device=self.dev)
+        st = self.torch.as_tensor(_DeviceArray(ptrs[1].value, (B,), '<i4'), device=self.dev)
+        return u0, st
+
+    def launch(self, u0, status, after=None):
+        torch = self.torch
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if after is not None:
+            self.side.wait_event(after)
+        with torch.cuda.stream(self.side):
+            g0.record()
+            self.pack[:, :4].copy_(u0)
+            self.pack[:, 4].copy_(status)
+            self.dist.all_gather_into_tensor(self.out, self.pack)
+            g1.record()
+        self.events.append((g0, g1))
+        self.launches += 3
+        self.last_local = (u0, status)
+
+    def drain(self):
+        """Wait for the outstanding gathers; returns the wait in ms (host clock)."""
+        t0 = time.perf_counter()
+        self.side.synchronize()
+        return (time.perf_counter() - t0) * 1e3
+
+    def mean_ms(self):
+        ms = [a.elapsed_time(b) for a, b in self.events[3:]]
+        return float(np.mean(ms)) if ms else None
+
+    def check(self, ctl):
+        """The slice of this rank inside the gathered tensor equals its local outputs."""
+        rank = self.dist.get_rank()
+        B = ctl.batch
+        mine = self.out[rank * B:(rank + 1) * B]
+        u0, st = self.last_local
+        return bool(self.torch.equal(mine[:, :4], u0) and
+                    self.torch.equal(mine[:, 4].to(self.torch.int32), st.to(self.torch.int32)))
+
+
 # ------------------------------------------------------------------ GPU arm
 def run_gpu(args):
     import torch
@@ -192,8 +263,15 @@ def run_gpu(args):
     params = load_params()
     params['solver']['max_sqp_iter'] = SQP_CAP
     params['solver']['sqp_tol'] = SQP_TOL
+    params['solver']['precision'] = args.dtype
+    if args.dtype == 'f32':
+        params['solver']['sqp_tol'] = 1e-4     # FP32 resolves steps to ~1e-5 (parity bar: 1e-3)
     ctl = BatchedPositionNMPC(params, batch=BATCH, device=local)
     hover = ctl.hover_thrust
+
+    # Multi-GPU: the (u0, status) all-gather north_star names, issued after every step's solve on a
+    # side stream so that it overlaps the next step (NCCL over NVLink 5 / NVSwitch).
+    gather = Gather(ctl, dev, world) if world > 1 else None
 
     # inputs: N_INPUT_SETS seeded batches per rank, resident in HBM and in pinned host memory
     dev_in, host_in = [], []
@@ -213,22 +291,22 @@ def run_gpu(args):
             dist.barrier()
         torch.cuda.synchronize(dev)
 
+    main = torch.cuda.current_stream(dev)
+
     def one_step(i, timed):
         x0, yref, yref_e = dev_in[i % N_INPUT_SETS]
         ctl.invalidate()          # cold start every step: each step is a fresh batch
         flush.zero_()             # evict the previous step's data from L2
-        torch.cuda.synchronize(dev)
-        if timed:
-            e0 = torch.cuda.Event(enable_timing=True)
-            e1 = torch.cuda.Event(enable_timing=True)
-            e0.record()
-            u0, st = ctl.solve(x0, yref, yref_e)
-            e1.record()
-            torch.cuda.synchronize(dev)
-            return e0.elapsed_time(e1), st
+        main.synchronize()        # (not the side stream: the previous step's gather may still run)
+        e0 = torch.cuda.Event(enable_timing=True)
+        e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
         u0, st = ctl.solve(x0, yref, yref_e)
-        torch.cuda.synchronize(dev)
-        return 0.0, st
+        e1.record()
+        if gather is not None:
+            gather.launch(u0, st, after=e1)
+        main.synchronize()
+        return (e0.elapsed_time(e1) if timed else 0.0), st
 
     W, K = max(args.warmup, 3), args.steps
     for i in range(W):
@@ -247,10 +325,13 @@ def run_gpu(args):
         qp_sum += int(stats['qp_iters'].sum())
         sqp_sum += int(stats['sqp_iters'].sum())
         ok_count += int((st == 0).sum().item())
+    drain_ms = gather.drain() if gather is not None else 0.0   # last gather(s) not yet complete
     barrier()
     wall = time.perf_counter() - wall0
-    launches = ctl.kernel_launches - launches0
-    total_ms = float(sum(step_ms))
+    launches = ctl.kernel_launches - launches0 + (gather.launches if gather is not None else 0)
+    total_ms = float(sum(step_ms)) + drain_ms
+    nccl_ms = gather.mean_ms() if gather is not None else None
+    gathered_ok = gather.check(ctl) if gather is not None else None
 
     # end-to-end through the public host API: pinned host buffers, H2D + solve + D2H per step
     e2e_t = []
@@ -258,12 +339,18 @@ def run_gpu(args):
         x0, yref, yref_e = host_in[i % N_INPUT_SETS]
         ctl.invalidate()
         flush.zero_()
-        torch.cuda.synchronize(dev)
+        main.synchronize()
         t0 = time.perf_counter()
         u0h, sth = ctl.solve(x0, yref, yref_e)     # returns after the D2H copies completed
+        if gather is not None:                     # device copies of the same outputs -> all ranks
+            gather.launch(*gather.handle_outputs(), after=None)
         t1 = time.perf_counter()
         if i >= W:
             e2e_t.append(t1 - t0)
+    if gather is not None:
+        t0 = time.perf_counter()
+        gather.drain()
+        e2e_t.append(time.perf_counter() - t0)
     e2e_total = float(sum(e2e_t))
     clocks = sampler.stop() if rank == 0 else None
 
@@ -280,6 +367,7 @@ def run_gpu(args):
         return 0
 
     n_solves = world * BATCH * K
+    is32 = args.dtype == 'f32'
     value = n_solves / (total_ms * 1e-3)
     e2e_value = n_solves / e2e_total
     mean_qp = qp_sum / n_solves
@@ -296,11 +384,15 @@ def run_gpu(args):
     hbm_peak = float(peaks.get('hbm_gbs', 6650.0))
     import ctypes as C
     tf = C.c_double(0.0)
-    _abi.check(_abi.lib().nmpc_fp64_peak(local, C.byref(tf)), 'nmpc_fp64_peak')
-    traffic = None
+    peak_fn = _abi.lib().nmpc_fp32_peak if is32 else _abi.lib().nmpc_fp64_peak
+    _abi.check(peak_fn(local, C.byref(tf)), 'nmpc_fp32_peak' if is32 else 'nmpc_fp64_peak')
+    traffic, traffic_src = None, None
     try:   # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of this workload's kernel,
-           # from the committed `ncu --set full` capture (profiles/, see its "source" field)
-        traffic = json.load(open(ROOT / 'profiles' / 'traffic.json'))['dram_bytes_per_launch']
+           # from the committed `ncu --set full` capture of this very command (written by
+           # scripts/ncu_traffic.py; its "source" and "head" fields say which capture and kernel)
+        tj = json.load(open(ROOT / 'profiles' / 'traffic.json'))
+        if tj.get('dtype', 'f64') == args.dtype:
+            traffic, traffic_src = tj['dram_bytes_per_launch'], tj.get('source')
     except Exception:
         pass
     achieved_gbs = bytes_per_launch / launch_s * 1e-9
@@ -309,7 +401,7 @@ def run_gpu(args):
         'metric': 'NMPC solves/sec (hummingbird, N=20)', 'value': value, 'unit': 'solves/s',
         'n_gpus': world, 'steps': K, 'warmup': W, 'ms_per_step': total_ms / K,
         'p50_batch_latency_ms': float(np.median(step_ms)),
-        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64',
+        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': args.dtype,
         'data': 'synthetic', 'config': workload_config(world),
         'clocks': clocks,
         'e2e': {'value': e2e_value, 'unit': 'solves/s',
@@ -318,11 +410,12 @@ def run_gpu(args):
         'gpu_launches': launches,
         # the bound that limits this kernel is the FP64 pipe (north_star: no tensor cores, FP64
         # FLOP/s and HBM GB/s against peak); the HBM roofline of the same launch is beside it
-        'roofline': {'bound': 'fp64', 'achieved': achieved_tf, 'peak': tf.value,
+        'roofline': {'bound': 'fp32' if is32 else 'fp64', 'achieved': achieved_tf, 'peak': tf.value,
                      'unit': 'TFLOP/s', 'frac': achieved_tf / tf.value if tf.value else None,
-                     'traffic': traffic,
-                     'peak_source': 'nmpc_fp64_peak: DFMA micro-benchmark on this GPU, same run '
-                                    '(MEASURED_PEAKS.json holds no FP64 figure)',
+                     'traffic': traffic, 'traffic_source': traffic_src,
+                     'peak_source': ('nmpc_fp32_peak: FFMA' if is32 else 'nmpc_fp64_peak: DFMA')
+                                    + ' micro-benchmark on this GPU, same run '
+                                    '(MEASURED_PEAKS.json holds no vector-FMA figure)',
                      'flops_per_solve': flops_per_launch / BATCH,
                      'note': 'algorithmic FP64 flops (DESIGN.md section 5) / CUDA-event launch time'},
         'roofline_hbm': {'bound': 'hbm', 'achieved': achieved_gbs, 'peak': hbm_peak, 'unit': 'GB/s',
@@ -333,6 +426,13 @@ def run_gpu(args):
                          'status_ok_frac': ok_count / n_solves},
         'wall_s_timed_region': wall,
     }
+    if is32:
+        line['parity'] = 'FP32 variant: u0 within 1e-3 relative of the FP64 oracle (tests/test_gpu_parity.py::test_fp32_variant), SQP step tolerance 1e-4'
+    if gather is not None:
+        line['nccl_ms_per_step'] = nccl_ms
+        line['nccl'] = {'collective': 'all_gather_into_tensor', 'bytes_per_rank_per_step': BATCH * 40,
+                        'stream': 'side stream, overlapped with the next step; drained inside the '
+                                  'timed region', 'gathered_equals_local': gathered_ok}
     if world == 1 and not args.no_cpu:
         cores = os.cpu_count() or 1
         n = 256 * cores if cores <= 32 else 128 * cores
@@ -341,7 +441,7 @@ def run_gpu(args):
             'value': v, 'unit': 'solves/s', 'cores': cores, 'kind': 'port',
             'sample': f'{n} problems of the same workload (seed 0), oracle/ C port, one process '
                       f'per core, {w:.1f} s wall'}
-    if world == 1 and not args.no_extras:
+    if world == 1 and not args.no_extras and not is32:
         line['extras'] = extras(params, dev)
     print(json.dumps(line), flush=True)
     if world > 1:
@@ -457,6 +557,22 @@ def extras(params, dev):
         'p50_latency_us': float(np.median(lat[20:]) * 1e6), 'p99_latency_us': float(np.percentile(lat[20:], 99) * 1e6),
         'final_position': [float(v) for v in x[0:3]], 'last_status': int(status)}
     one.close()
+    # the same closed loop through the CPU oracle's PositionNMPC-shaped wrapper on ONE host core:
+    # configs[0] is the reference's own (latency) case, so this is the baseline beside it
+    from oracle import oracle as O
+    orc = O.OraclePositionNMPC(p1)
+    x = np.array([0, 0, 1, 0, 0, 0, 1, 0, 0, 0, 0, 0, 0], float)
+    lat_o = []
+    for step in range(120):
+        state = {'position': x[0:3], 'velocity': x[3:6], 'quaternion': x[6:10], 'body_rates': x[10:13]}
+        t0 = time.perf_counter()
+        u0, status = orc.solve(state, horizon)
+        lat_o.append(time.perf_counter() - t0)
+        thrust = np.clip(u0, *[np.asarray(b) for b in (orc.cfg.lbu[:], orc.cfg.ubu[:])])
+        x = O.plant_step(orc.cfg, x, thrust, orc.cfg.dt, 5)
+    out['single_vehicle_rti']['cpu_oracle_p50_latency_us'] = float(np.median(lat_o[20:]) * 1e6)
+    out['single_vehicle_rti']['cpu_oracle_p99_latency_us'] = float(np.percentile(lat_o[20:], 99) * 1e6)
+    out['single_vehicle_rti']['cpu_oracle_final_position'] = [float(v) for v in x[0:3]]
     return out
 
 
@@ -466,6 +582,8 @@ def main():
     ap.add_argument('--steps', type=int, default=40)
     ap.add_argument('--warmup', type=int, default=5)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--dtype', default='f64', choices=['f64', 'f32'],
+                    help='compute precision of the solve kernel (I/O stays FP64)')
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
     ap.add_argument('--no-extras', action='store_true',
                     help='skip the large-batch RTI / closed-loop context numbers')

@@ -235,6 +235,8 @@ int nmpc_last_outputs(nmpc_handle_t *h, const double **u0, const int32_t **statu
 /* Measured DFMA throughput of `device` in TFLOP/s (8 independent FMA chains per thread,
  * best of 4): the FP64 roofline denominator used by bench.py. */
 int nmpc_fp64_peak(int32_t device, double *tflops);
+/* FFMA twin: the FP32 roofline denominator of the FP32 variant (bench.py --dtype f32). */
+int nmpc_fp32_peak(int32_t device, double *tflops);
 
 /* Debug aid standing in for compute-sanitizer's initcheck (the tool is closed on this GPU pool):
  * with `on`, every launch first fills the whole workspace with NaN and the kernel fills its

@@ -85,6 +85,7 @@ SYMBOLS = {
     'nmpc_last_outputs': (C.c_int, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp),
                                     C.POINTER(_vp)]),
     'nmpc_fp64_peak': (C.c_int, [C.c_int32, C.POINTER(C.c_double)]),
+    'nmpc_fp32_peak': (C.c_int, [C.c_int32, C.POINTER(C.c_double)]),
     'nmpc_debug_poison': (C.c_int, [_vp, C.c_int32]),
     'nmpc_batch': (C.c_int, [_vp]),
     'nmpc_horizon': (C.c_int, [_vp]),

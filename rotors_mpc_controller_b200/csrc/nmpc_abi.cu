@@ -126,6 +126,26 @@ __global__ void __launch_bounds__(256) fp64_peak_kernel(double* out, int iters, 
   out[blockIdx.x * blockDim.x + threadIdx.x] = v0 + v1 + v2 + v3 + v4 + v5 + v6 + v7;
 }
 
+// FFMA twin of fp64_peak_kernel (FP32 roofline denominator of the FP32 variant).
+__global__ void __launch_bounds__(256) fp32_peak_kernel(float* out, int iters, float a, float b) {
+  float v0 = threadIdx.x, v1 = v0 + 1, v2 = v0 + 2, v3 = v0 + 3, v4 = v0 + 4, v5 = v0 + 5,
+        v6 = v0 + 6, v7 = v0 + 7;
+  for (int i = 0; i < iters; i++) {
+#pragma unroll
+    for (int r = 0; r < 8; r++) {
+      v0 = fmaf(v0, a, b);
+      v1 = fmaf(v1, a, b);
+      v2 = fmaf(v2, a, b);
+      v3 = fmaf(v3, a, b);
+      v4 = fmaf(v4, a, b);
+      v5 = fmaf(v5, a, b);
+      v6 = fmaf(v6, a, b);
+      v7 = fmaf(v7, a, b);
+    }
+  }
+  out[blockIdx.x * blockDim.x + threadIdx.x] = v0 + v1 + v2 + v3 + v4 + v5 + v6 + v7;
+}
+
 thread_local char g_err[512] = "";
 
 template <typename T>
@@ -789,6 +809,37 @@ int nmpc_fp64_peak(int32_t device, double* tflops) {
   for (int rep = 0; rep < 5; rep++) {
     CK(cudaEventRecord(e0));
     fp64_peak_kernel<<<blocks, threads>>>(buf, iters, 1.0000001, 1e-9);
+    CK(cudaEventRecord(e1));
+    CK(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, e0, e1));
+    const double flops = 2.0 * 64.0 * iters * (double)blocks * threads;
+    if (rep > 0 && flops / (ms * 1e-3) * 1e-12 > best) best = flops / (ms * 1e-3) * 1e-12;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(buf);
+  *tflops = best;
+  return NMPC_OK;
+}
+
+int nmpc_fp32_peak(int32_t device, double* tflops) {
+  if (!tflops) return NMPC_E_INVALID;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) return NMPC_E_NODEVICE;
+  CK(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, device));
+  const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 8192;
+  float* buf = nullptr;
+  CK(cudaMalloc(&buf, (size_t)blocks * threads * sizeof(float)));
+  cudaEvent_t e0, e1;
+  CK(cudaEventCreate(&e0));
+  CK(cudaEventCreate(&e1));
+  double best = 0.0;
+  for (int rep = 0; rep < 5; rep++) {
+    CK(cudaEventRecord(e0));
+    fp32_peak_kernel<<<blocks, threads>>>(buf, iters, 1.0000001f, 1e-9f);
     CK(cudaEventRecord(e1));
     CK(cudaEventSynchronize(e1));
     float ms = 0.f;
