@@ -119,13 +119,14 @@ def run_reference(args):
     return 0
 
 
-def workload_config(gpus):
+def workload_config(gpus, dtype='f64'):
     par = (f'batch-sharded x{gpus}; per step an NCCL all-gather of (u0[4], status) per problem '
            f'(40 B) on a side stream, overlapped with the next step' if gpus > 1
            else 'single GPU (batch-sharded x1, nothing to gather)')
     return {'workload': 'configs[1]: batch 4096 hummingbirds per GPU, randomised states around '
                         'hover, random set-point steps, N=20, dt=0.05, cold start, SQP to '
-                        'convergence (step<=1e-8, cap 50), ERK midpoint x2, u-box [0.0214,6.003] N',
+                        f'convergence (step<={"1e-4" if dtype == "f32" else "1e-8"}, cap 50), ERK midpoint x2, '
+                        'u-box [0.0214,6.003] N',
             'batch_per_gpu': BATCH, 'horizon': HORIZON, 'global_batch': BATCH * gpus,
             'parallelism': par,
             'l2': 'flushed between timed steps (256 MiB write, outside the event pair)'}
@@ -402,7 +403,7 @@ def run_gpu(args):
         'n_gpus': world, 'steps': K, 'warmup': W, 'ms_per_step': total_ms / K,
         'p50_batch_latency_ms': float(np.median(step_ms)),
         'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': args.dtype,
-        'data': 'synthetic', 'config': workload_config(world),
+        'data': 'synthetic', 'config': workload_config(world, args.dtype),
         'clocks': clocks,
         'e2e': {'value': e2e_value, 'unit': 'solves/s',
                 'h2d_bytes_per_step': BATCH * (13 + HORIZON * 17 + 13) * 8,
@@ -510,7 +511,8 @@ def extras(params, dev):
                                         + float(st['qp_iters'].mean()) * F_IPM) / (med * 1e-3) * 1e-12}
     cs.close()
     # closed loop: 65536 vehicles x 50 control steps, warm-started RTI, RK4 plant on the device
-    cl = ClosedLoop(ctl, Plant(dt=ctl.dt, substeps=5))
+    rate = float(params.get('node', {}).get('rate', 60.0))     # the node re-solves at 60 Hz
+    cl = ClosedLoop(ctl, Plant(dt=1.0 / rate, substeps=5))
     rng = np.random.default_rng(1)
     x = random_states(rng, B)
     sp = x[:, 0:3] + np.concatenate([rng.uniform(-2, 2, (B, 2)), rng.uniform(-0.5, 0.5, (B, 1))], 1)
@@ -526,7 +528,8 @@ def extras(params, dev):
     torch.cuda.synchronize(dev)
     ms = e0.elapsed_time(e1)
     s = cl.summary(reduce=False)
-    out['closed_loop_rti'] = {'vehicles': B, 'steps': steps, 'solves_per_s': B * steps / (ms * 1e-3),
+    out['closed_loop_rti'] = {'vehicles': B, 'steps': steps, 'control_rate_hz': rate,
+                              'solves_per_s': B * steps / (ms * 1e-3),
                               'ms_per_control_step': ms / steps,
                               'mean_factorisations': s['qp_iters'] / (B * steps),
                               'failed_solves': s['failed_solves']}

@@ -193,6 +193,13 @@ typedef struct nmpc_plant {
   double tau_down;
   double rotor_drag;   /* rotor_drag_coefficient (gazebo_motor_model.cpp:443-453), 0 = off */
   double mass;         /* plant mass; <= 0 means the controller's */
+  double rolling_moment; /* rolling_moment_coefficient (gazebo_motor_model.cpp:470-474,
+                          hummingbird.xacro:42: 1e-6): world-frame torque -sum|w_i| mu v_perp; 0 = off */
+  int32_t rotors_yaw_sign; /* 0: yaw torque with the CONTROLLER's sign (controller.py:102-103,328:
+                          nominal plant, the loop is well posed); 1: RotorS' sign, drag torque
+                          -turning_direction * thrust * km (gazebo_motor_model.cpp:458-459,
+                          rotors_control common.h:92-93) -- the reference's real model mismatch */
+  int32_t reserved0;   /* must be 0 */
 } nmpc_plant_t;
 
 /* One control interval for every problem: x[batch,13] (in/out, quaternion left as integrated),

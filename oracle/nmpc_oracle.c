@@ -228,8 +228,21 @@ void orc_plant_step(const orc_config *c, const double *x, const double *u, doubl
 void orc_plant_step_ext(const orc_config *c, const double *x, const double *u, double dt,
                         int substeps, int motor_model, double tau_up, double tau_down,
                         double rotor_drag, double mass, double *rotor, double *xn) {
+  orc_plant_step_full(c, x, u, dt, substeps, motor_model, tau_up, tau_down, rotor_drag, mass, 0.0, 0,
+                      rotor, xn);
+}
+
+/* + rolling moment -sum|w_i| mu_1 v_perp as a world-frame torque (gazebo_motor_model.cpp:470-474,
+ * coefficient hummingbird.xacro:42) and the plant-side yaw-torque sign (:458-459; opposite to the
+ * controller's, controller.py:102-103): the reference's real model mismatch, opt-in. */
+void orc_plant_step_full(const orc_config *c, const double *x, const double *u, double dt,
+                         int substeps, int motor_model, double tau_up, double tau_down,
+                         double rotor_drag, double mass, double rolling_moment, int rotors_yaw_sign,
+                         double *rotor, double *xn) {
   orc_config cp = *c;
   if (mass > 0.0) cp.mass = mass;
+  if (rotors_yaw_sign)
+    for (int i = 0; i < NU; i++) cp.rotor_z[i] = -c->rotor_z[i];
   double xc[NX], w[NU], wcmd[NU];
   memcpy(xc, x, sizeof(xc));
   const double h = dt / (double)(substeps > 0 ? substeps : 1);
@@ -260,6 +273,19 @@ void orc_plant_step_ext(const orc_config *c, const double *x, const double *u, d
         k[st][3] -= kd * (t[3] - vz * zx);
         k[st][4] -= kd * (t[4] - vz * zy);
         k[st][5] -= kd * (t[5] - vz * zz);
+      }
+      if (rolling_moment != 0.0) {
+        const double qw = t[6], qx = t[7], qy = t[8], qz = t[9];
+        const double R[3][3] = {
+            {1.0 - 2.0 * (qy * qy + qz * qz), 2.0 * (qx * qy - qw * qz), 2.0 * (qx * qz + qw * qy)},
+            {2.0 * (qx * qy + qw * qz), 1.0 - 2.0 * (qx * qx + qz * qz), 2.0 * (qy * qz - qw * qx)},
+            {2.0 * (qx * qz - qw * qy), 2.0 * (qy * qz + qw * qx), 1.0 - 2.0 * (qx * qx + qy * qy)}};
+        const double vz = t[3] * R[0][2] + t[4] * R[1][2] + t[5] * R[2][2];
+        const double kk = -saw * rolling_moment;
+        const double tw[3] = {kk * (t[3] - vz * R[0][2]), kk * (t[4] - vz * R[1][2]),
+                              kk * (t[5] - vz * R[2][2])};
+        for (int a = 0; a < 3; a++)
+          k[st][10 + a] += (R[0][a] * tw[0] + R[1][a] * tw[1] + R[2][a] * tw[2]) / cp.J[a];
       }
     }
     for (int i = 0; i < NX; i++)

@@ -164,6 +164,11 @@ void orc_plant_step_ext(const orc_config *c, const double *x, const double *u, d
                         int substeps, int motor_model, double tau_up, double tau_down,
                         double rotor_drag, double mass, double *rotor, double *xn);
 
+void orc_plant_step_full(const orc_config *c, const double *x, const double *u, double dt,
+                         int substeps, int motor_model, double tau_up, double tau_down,
+                         double rotor_drag, double mass, double rolling_moment, int rotors_yaw_sign,
+                         double *rotor, double *xn);
+
 #ifdef __cplusplus
 }
 #endif

@@ -272,16 +272,17 @@ class OraclePositionNMPC:
 
 # ------------------------------------------------------------------ closed loop (f1-f3 checkers)
 def plant_step_ext(cfg, x, u, dt, substeps=1, motor_model=0, tau_up=0.0125, tau_down=0.025,
-                   rotor_drag=0.0, mass=0.0, rotor=None):
-    """orc_plant_step_ext: returns (xn, rotor_speed_new)."""
+                   rotor_drag=0.0, mass=0.0, rotor=None, rolling_moment=0.0, rotors_yaw_sign=False):
+    """orc_plant_step_full: returns (xn, rotor_speed_new)."""
     xn = np.zeros(NX)
     rot = np.zeros(NU) if rotor is None else np.ascontiguousarray(rotor, float).copy()
-    lib().orc_plant_step_ext.restype = None
-    lib().orc_plant_step_ext(C.byref(cfg), _p(np.ascontiguousarray(x, float)),
-                             _p(np.ascontiguousarray(u, float)), C.c_double(dt),
-                             C.c_int(substeps), C.c_int(motor_model), C.c_double(tau_up),
-                             C.c_double(tau_down), C.c_double(rotor_drag), C.c_double(mass),
-                             _p(rot), _p(xn))
+    lib().orc_plant_step_full.restype = None
+    lib().orc_plant_step_full(C.byref(cfg), _p(np.ascontiguousarray(x, float)),
+                              _p(np.ascontiguousarray(u, float)), C.c_double(dt),
+                              C.c_int(substeps), C.c_int(motor_model), C.c_double(tau_up),
+                              C.c_double(tau_down), C.c_double(rotor_drag), C.c_double(mass),
+                              C.c_double(rolling_moment), C.c_int(int(bool(rotors_yaw_sign))),
+                              _p(rot), _p(xn))
     return xn, rot
 
 
@@ -362,7 +363,8 @@ def closed_loop(cfg, x_init, steps, ref_fn, pref_fn, plant=None, rotor_init=None
     nmpc_rollout_device.  ref_fn(k) -> (yref, yref_e); pref_fn(k) -> p_ref[B,3] the error of the
     NEW state is measured against.  Returns (x, stats[B,8], rotor, last outputs)."""
     plant = {**dict(dt=cfg.dt, substeps=1, motor_model=0, tau_up=0.0125, tau_down=0.025,
-                    rotor_drag=0.0, mass=0.0), **(plant or {})}
+                    rotor_drag=0.0, mass=0.0, rolling_moment=0.0, rotors_yaw_sign=False),
+             **(plant or {})}
     x = np.array(x_init, float).reshape(-1, NX).copy()
     B = x.shape[0]
     ob = OracleBatch(cfg, B)
@@ -380,7 +382,8 @@ def closed_loop(cfg, x_init, steps, ref_fn, pref_fn, plant=None, rotor_init=None
         for b in range(B):
             x[b], rot = plant_step_ext(cfg, x[b], thrust[b], plant['dt'], plant['substeps'],
                                        plant['motor_model'], plant['tau_up'], plant['tau_down'],
-                                       plant['rotor_drag'], plant['mass'], rotor[b])
+                                       plant['rotor_drag'], plant['mass'], rotor[b],
+                                       plant['rolling_moment'], plant['rotors_yaw_sign'])
             if plant['motor_model']:
                 rotor[b] = rot
         e = np.linalg.norm(x[:, 0:3] - pref, axis=1)

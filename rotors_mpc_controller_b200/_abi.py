@@ -46,7 +46,8 @@ class NmpcPlant(C.Structure):
     """Mirror of ``nmpc_plant_t``."""
     _fields_ = [('substeps', C.c_int32), ('motor_model', C.c_int32), ('dt', C.c_double),
                 ('tau_up', C.c_double), ('tau_down', C.c_double), ('rotor_drag', C.c_double),
-                ('mass', C.c_double)]
+                ('mass', C.c_double), ('rolling_moment', C.c_double),
+                ('rotors_yaw_sign', C.c_int32), ('reserved0', C.c_int32)]
 
 
 class NmpcRollout(C.Structure):

@@ -10,7 +10,8 @@ moving track); states, references, warm starts and commands never leave HBM.
 The plant is the controller's own model (``controller.py:286-346``) integrated with RK4; the
 first-order rotor-speed lag and rotor drag of RotorS' motor model
 (``rotors_gazebo_plugins/src/gazebo_motor_model.cpp:415-483``, ``common.h:147-183``) are optional.
-Gazebo's rigid-body engine, rolling moment and sensor noise are not restated.
+the rolling moment (``:470-474``) and RotorS' own yaw-torque sign (``:458-459``) as well -- the
+opt-in "model-mismatch" plant.  Gazebo's rigid-body engine and sensor noise are not restated.
 """
 from __future__ import annotations
 
@@ -46,13 +47,17 @@ class Plant:
     tau_up: float = 0.0125          # rotors_description/urdf/hummingbird.xacro:29-46
     tau_down: float = 0.025
     rotor_drag: float = 0.0         # 8.06428e-05 in hummingbird.xacro
-    mass: float = 0.0               # <= 0: the controller's mass
+    mass: float = 0.0               # <= 0: the controller's mass (RotorS: 0.716 = 0.68 + 4 x 0.009)
+    rolling_moment: float = 0.0     # 1e-06 in hummingbird.xacro:42
+    rotors_yaw_sign: bool = False   # True: RotorS' yaw-torque sign (opposite to the controller's)
 
     def to_c(self) -> _abi.NmpcPlant:
         p = _abi.NmpcPlant()
         p.substeps, p.motor_model, p.dt = int(self.substeps), int(self.motor_model), float(self.dt)
         p.tau_up, p.tau_down = float(self.tau_up), float(self.tau_down)
         p.rotor_drag, p.mass = float(self.rotor_drag), float(self.mass)
+        p.rolling_moment = float(self.rolling_moment)
+        p.rotors_yaw_sign, p.reserved0 = int(bool(self.rotors_yaw_sign)), 0
         return p
 
 

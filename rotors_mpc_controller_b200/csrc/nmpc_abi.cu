@@ -654,6 +654,8 @@ static PlantCfg make_plantcfg(const nmpc_handle* h, const nmpc_plant_t& p) {
   pc.tau_down = p.tau_down;
   pc.rotor_drag = p.rotor_drag;
   pc.inv_mass = 1.0 / (p.mass > 0.0 ? p.mass : h->cfg.mass);
+  pc.rolling_moment = p.rolling_moment;
+  pc.rotors_yaw_sign = p.rotors_yaw_sign ? 1 : 0;
   return pc;
 }
 
@@ -661,6 +663,7 @@ static int validate_plant(const nmpc_plant_t* p, const double* rotor_speed) {
   if (!p || p->substeps < 0 || p->substeps > 100000) return NMPC_E_INVALID;
   if (p->substeps > 0 && !(p->dt > 0.0)) return NMPC_E_INVALID;
   if (p->motor_model != 0 && p->motor_model != 1) return NMPC_E_INVALID;
+  if (!(p->rolling_moment >= 0.0) || !(p->rotor_drag >= 0.0)) return NMPC_E_INVALID;
   if (p->motor_model == 1 && (!rotor_speed || !(p->tau_up > 0.0) || !(p->tau_down > 0.0)))
     return NMPC_E_INVALID;
   return NMPC_OK;

@@ -131,8 +131,8 @@ __global__ void __launch_bounds__(128)
 
 // Plant parameters (host-filled; mirrors nmpc_plant_t of include/nmpc_b200.h).
 struct PlantCfg {
-  int substeps, motor_model;
-  double dt, tau_up, tau_down, rotor_drag, inv_mass;
+  int substeps, motor_model, rotors_yaw_sign;
+  double dt, tau_up, tau_down, rotor_drag, inv_mass, rolling_moment;
 };
 
 // Controller model + optional rotor drag (gazebo_motor_model.cpp:443-453):
@@ -150,6 +150,23 @@ __device__ __forceinline__ void plant_f(const DevCfg<double>& c, const PlantCfg&
     f[3] -= k * (x[3] - vz * zx);
     f[4] -= k * (x[4] - vz * zy);
     f[5] -= k * (x[5] - vz * zz);
+  }
+  if (pc.rolling_moment != 0.0) {
+    // rolling moment (gazebo_motor_model.cpp:470-474): world-frame torque -sum|w_i| mu_1 v_perp on
+    // the body; into the body frame with R(q)' (rotation of controller.py:294-302), then J^-1
+    const double qw = x[6], qx = x[7], qy = x[8], qz = x[9];
+    const double r11 = 1.0 - 2.0 * (qy * qy + qz * qz), r12 = 2.0 * (qx * qy - qw * qz),
+                 r13 = 2.0 * (qx * qz + qw * qy);
+    const double r21 = 2.0 * (qx * qy + qw * qz), r22 = 1.0 - 2.0 * (qx * qx + qz * qz),
+                 r23 = 2.0 * (qy * qz - qw * qx);
+    const double r31 = 2.0 * (qx * qz - qw * qy), r32 = 2.0 * (qy * qz + qw * qx),
+                 r33 = 1.0 - 2.0 * (qx * qx + qy * qy);
+    const double vz = x[3] * r13 + x[4] * r23 + x[5] * r33;
+    const double k = -sum_abs_w * pc.rolling_moment;
+    const double tx = k * (x[3] - vz * r13), ty = k * (x[4] - vz * r23), tz = k * (x[5] - vz * r33);
+    f[10] += (r11 * tx + r21 * ty + r31 * tz) * c.invJ[0];
+    f[11] += (r12 * tx + r22 * ty + r32 * tz) * c.invJ[1];
+    f[12] += (r13 * tx + r23 * ty + r33 * tz) * c.invJ[2];
   }
 }
 
@@ -191,6 +208,10 @@ __global__ void __launch_bounds__(128)
   }
   DevCfg<double> cp = c;  // plant mass may differ from the controller's
   cp.inv_mass = pc.inv_mass;
+  if (pc.rotors_yaw_sign) {  // RotorS' drag-torque sign (gazebo_motor_model.cpp:458-459)
+#pragma unroll
+    for (int i = 0; i < NU; i++) cp.rz[i] = -c.rz[i];
+  }
   const double h = pc.dt / (double)(pc.substeps > 0 ? pc.substeps : 1);
   double wcmd[NU];
   if (pc.motor_model) {

@@ -7,7 +7,8 @@
 
 Every trajectory: random initial state around hover (SURVEY 8d cfg2 distribution), set-point step
 at t=0 (or a figure-8 track with --figure8), `steps` control steps of SQP-RTI with warm start and
-last-valid fallback, nominal RK4 plant.  Rank g owns the contiguous slice [g*B/G, (g+1)*B/G) for
+last-valid fallback, nominal RK4 plant, re-solved at the node's rate (60 Hz, params.yaml node.rate;
+--control-rate 20 steps the plant by the solver dt instead).  Rank g owns the contiguous slice [g*B/G, (g+1)*B/G) for
 the whole run; the only communication is the final reduction of the statistics vector.
 Prints one JSON line on rank 0.
 """
@@ -31,8 +32,14 @@ def main():
     ap.add_argument('--trajectories', type=int, default=131072)
     ap.add_argument('--steps', type=int, default=200)
     ap.add_argument('--substeps', type=int, default=5)
+    ap.add_argument('--control-rate', type=float, default=None,
+                    help='re-solve rate in Hz (default: node.rate of params.yaml = 60 Hz, the '
+                         'reference node; the horizon keeps the solver dt = 0.05 s)')
     ap.add_argument('--figure8', action='store_true')
     ap.add_argument('--motor-lag', action='store_true')
+    ap.add_argument('--rotors-plant', action='store_true',
+                    help="RotorS-faithful model-mismatch plant: motor lag, rotor drag, rolling "
+                         "moment 1e-6, mass 0.716 kg and RotorS' yaw-torque sign (SURVEY Q3, Q5)")
     ap.add_argument('--chunk', type=int, default=131072, help='vehicles per handle (HBM bound)')
     ap.add_argument('--precision', default='f64')
     args = ap.parse_args()
@@ -55,11 +62,15 @@ def main():
 
     params = yaml.safe_load(open(default_params_path()))
     params['solver']['precision'] = args.precision
+    rate = args.control_rate or float(params.get('node', {}).get('rate', 60.0))   # mpc_controller_node:55
     lo, hi = shard_bounds(rank, world, args.trajectories)
     n_local = hi - lo
     plant_kw = dict(substeps=args.substeps)
     if args.motor_lag:
         plant_kw.update(motor_model=1, rotor_drag=8.06428e-5)
+    if args.rotors_plant:   # hummingbird.xacro:29-46, gazebo_motor_model.cpp:415-483
+        plant_kw.update(motor_model=1, rotor_drag=8.06428e-5, rolling_moment=1e-6, mass=0.716,
+                        rotors_yaw_sign=True)
 
     agg = np.zeros(9)
     mx = np.zeros(2)
@@ -73,7 +84,7 @@ def main():
             if ctl is not None:
                 ctl.close()
             ctl = BatchedPositionNMPC(params, batch=b, device=local)
-            cl = ClosedLoop(ctl, Plant(dt=ctl.dt, **plant_kw))
+            cl = ClosedLoop(ctl, Plant(dt=1.0 / rate, **plant_kw))
         rng = np.random.default_rng([rank, done])
         x = random_states(rng, b)
         cl.reset(x)
@@ -116,7 +127,7 @@ def main():
             'nonfinite': int(t[7]), 'saturated_step_frac': t[5] / solves,
             'rms_pos_err': float(np.sqrt(t[1] / solves)), 'mean_final_pos_err': t[2] / n,
             'max_final_pos_err': m[1], 'precision': args.precision,
-            'plant': plant_kw}), flush=True)
+            'plant': plant_kw, 'control_rate_hz': rate, 'horizon_dt': params['solver']['dt']}), flush=True)
     if world > 1:
         dist.destroy_process_group()
 

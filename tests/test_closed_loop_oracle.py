@@ -106,3 +106,33 @@ def test_closed_loop_oracle_converges(built, params):
     assert np.all(stats[:, 2] == 0) and np.all(stats[:, 7] == 0)
     assert np.all(stats[:, 1] < 0.05) and np.all(stats[:, 5] <= 2.07)
     assert np.allclose(np.linalg.norm(xf[:, 0:3] - sp, axis=1), stats[:, 1])
+
+
+def test_plant_rolling_moment_and_rotors_yaw_sign(built, params):
+    """f1 model-mismatch terms against an independent numpy restatement of
+    gazebo_motor_model.cpp:458-474: the body-rate derivative gains J^-1 R' (-sum|w| mu v_perp) and
+    the yaw drag torque flips sign; everything else of the step is unchanged."""
+    O, cfg = _cfg(params)
+    rng = np.random.default_rng(5)
+    J = np.array(cfg.J[:])
+    for _ in range(10):
+        x = random_states(rng, 1, tilt_deg=40.0, v_sigma=2.0)[0]
+        u = rng.uniform(0.5, 5.0, 4)
+        h = 1e-7                                   # one RK4 step of 0.1 us: x+ = x + h f to O(h^2)
+        base, _ = O.plant_step_ext(cfg, x, u, h)
+        mu = 1e-3
+        roll, _ = O.plant_step_ext(cfg, x, u, h, rolling_moment=mu)
+        yaw, _ = O.plant_step_ext(cfg, x, u, h, rotors_yaw_sign=True)
+        w, qx, qy, qz = x[6:10]
+        R = np.array([[1 - 2 * (qy * qy + qz * qz), 2 * (qx * qy - w * qz), 2 * (qx * qz + w * qy)],
+                      [2 * (qx * qy + w * qz), 1 - 2 * (qx * qx + qz * qz), 2 * (qy * qz - w * qx)],
+                      [2 * (qx * qz - w * qy), 2 * (qy * qz + w * qx), 1 - 2 * (qx * qx + qy * qy)]])
+        v = x[3:6]
+        vperp = v - (v @ R[:, 2]) * R[:, 2]
+        saw = np.sum(np.sqrt(u / cfg.kf))
+        dw = (R.T @ (-saw * mu * vperp)) / J
+        assert np.max(np.abs((roll - base)[10:13] / h - dw)) < 1e-5 * max(1.0, np.abs(dw).max())
+        assert np.max(np.abs((roll - base)[:10])) < 1e-10          # second order in h
+        tz = u @ np.array(cfg.rotor_z[:])
+        assert abs((yaw - base)[12] / h - (-2.0 * tz / J[2])) < 1e-5 * max(1.0, abs(tz / J[2]))
+        assert np.max(np.abs((yaw - base)[:12])) < 1e-10

@@ -65,7 +65,11 @@ def test_odometry_to_state(params, O):
 
 @pytest.mark.parametrize('plant', [dict(substeps=1), dict(substeps=50),
                                    dict(substeps=10, motor_model=1, rotor_drag=8.06428e-5,
-                                        mass=0.716)])
+                                        mass=0.716),
+                                   # the RotorS-faithful "model-mismatch" plant
+                                   dict(substeps=10, motor_model=1, rotor_drag=8.06428e-5,
+                                        mass=0.716, rolling_moment=1e-6, rotors_yaw_sign=True),
+                                   dict(substeps=4, rolling_moment=1e-3)])
 def test_plant_step(params, O, plant):
     B = 48
     cl, ctl, p = _mk(params, B, plant=plant)
