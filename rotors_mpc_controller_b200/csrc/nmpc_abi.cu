@@ -16,13 +16,14 @@ using namespace nmpc;
 
 namespace {
 
-// One warp per CTA (warps never synchronise with each other).  The register file is partitioned
+// CTAs of four independent warps (warps never synchronise with each other; 3 CTAs of 4 x 10.3 KB
+// tiles fit the 132 KB shared-memory configuration).  The register file is partitioned
 // per scheduler (16 K registers each): 3 warps per scheduler = 12 problems in flight per SM fit up
 // to 170 registers, 4 per scheduler need <= 128 (FP32 kernels do, FP64 ones spill in the sweeps and
 // lose more than the extra warps bring).  The FP64 cap is set a little below what ptxas would take
 // (156): the 160-register schedule measures 4-5 % faster than the unconstrained one.
 #ifndef NMPC_WARPS
-#define NMPC_WARPS 1
+#define NMPC_WARPS 4
 #endif
 #ifndef NMPC_MAXNREG
 #define NMPC_MAXNREG 160
@@ -51,8 +52,6 @@ __global__ void __maxnreg__(sizeof(T) == 4 ? NMPC_MAXNREG_F32 : NMPC_MAXNREG)
   }
   const int slot = blockIdx.x * WARPS + warp;
   T* ws = A.ws + (size_t)slot * L.total;
-  init_position_columns(NF > 0 ? NF : A.cfg.N, ws, L, lane);  // constant columns e_a of every A_k
-  __syncwarp();
   // dynamic work queue: iteration counts differ per problem, so problems are handed out one
   // at a time instead of in a fixed stride
   for (;;) {

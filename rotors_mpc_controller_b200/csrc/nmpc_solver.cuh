@@ -57,10 +57,20 @@ struct WsLayout {
 };
 
 // One record per stage keeps what the sweeps stream together contiguous (one 16-byte-chunked
-// cp.async range per stage): M_k at L.M + k*REC, K_k at L.K + k*REC.
-constexpr int M_LD = NZ + 1;             // 18: row [B_k | A_k | b_k] (rows start 16-byte aligned)
-constexpr int REC_K = NX * M_LD;         // 234: offset of K_k inside a record
-constexpr int REC = REC_K + NU * NX;     // 286
+// cp.async range per stage): [ M_k | K_k | LDL' factors of Quu_k ].
+// Nothing in the model depends on the position or the velocity (controller.py:286-346), so the
+// p and v columns of every A_k are the constants [I; 0; 0; 0] and [dt I; I; 0; 0]: they are never
+// stored, every sweep synthesises them in registers.  A row of M_k is therefore
+//     [ B_k(i, 0..3) | A_k(i, q0..q3) | A_k(i, w0..w2) | b_k(i) ]        12 elements, 16-byte aligned
+// (the defect b_k rides in the last column, so the right-hand side travels with the tile).
+constexpr int M_LD = 12;
+constexpr int MC_Q = 4, MC_W = 8, MC_B = 11;  // first q / w column and the defect column of a row
+constexpr int REC_K = NX * M_LD;              // 156: offset of K_k inside a record
+constexpr int K_LD = 14;                      // rows of K_k (4 x 13) padded to 16-byte multiples
+constexpr int REC_F = REC_K + NU * K_LD;      // 212: offset of the factors (10 used of 16)
+constexpr int REC = REC_F + 16;               // 228 elements per stage
+// column of a row of M_k that holds dx+/d(state j), j = 6..12 (q, w)
+__host__ __device__ constexpr int mcol_of_state(int j) { return j - 6 + MC_Q; }
 
 __host__ __device__ inline WsLayout make_layout(int N) {
   WsLayout L;
@@ -72,9 +82,9 @@ __host__ __device__ inline WsLayout make_layout(int N) {
     return r;
   };
   const int nx = (N + 1) * NX, nu = N * NU;
-  L.M = take(N * REC);  // stage records [M_k | b_k (13 rows of 17+1) | K_k (4x13)], REC each
+  L.M = take(N * REC);  // stage records [M_k (13 x 12) | K_k (4 x 14) | factors (16)], REC each
   L.K = L.M + REC_K;
-  L.Qi = take(N * 16);
+  L.Qi = L.M + REC_F;
   L.kff = take(nu);
   L.kffd = take(nu);
   L.xb = take(nx);
@@ -119,19 +129,22 @@ __host__ __device__ inline WsLayout make_layout(int N) {
   (void)N;
 
 // Per-warp shared-memory tile (elements of T).
-constexpr int SP_LD = 14;  // padded leading dimension of P and K rows (16-byte aligned rows)
+constexpr int SP_LD = 14;  // padded leading dimension of P rows (16-byte aligned rows)
+constexpr int RING = 4;    // stage records in flight per sweep: cp.async runs 3 stages ahead, which
+                           // covers an L2 round trip (~800 cycles) with the ~250 cycles of a roll-out stage
 struct SmemLayout {
   static constexpr int P = 0;                    // 13 x 14 cost-to-go + a zero row (dummy W row)
   static constexpr int M = P + (NX + 1) * SP_LD; // stage buffers of the sweeps (cp.async targets):
-                                                 //   factor: 2 x 234 + 224, forward: 2 x 286
-  static constexpr int K = M + 692;              // 4 x 14
+                                                 //   factor: 2 x 156 + 224 (W), others: RING x 228
+  static constexpr int K = M + RING * REC;       // 4 x 14
   static constexpr int p = K + NU * SP_LD;       // 13 (+1)
   static constexpr int wv = p + 14;              // 13 (+1)
   static constexpr int xA = wv + 14;             // 13 (+1) forward-sweep state, ping
   static constexpr int xB = xA + 14;             // pong
   static constexpr int bar = xB + 14;            // mbarrier of the input staging + its parity
   static constexpr int G = bar + 4;              // 16 x 4 exchange tile of factor_sweep + 4 (g_u)
-  static constexpr int total = G + 68;           // 1072 elements
+  static constexpr int S = G + 68;               // RING x 8 per-stage scalars of the streaming sweeps
+  static constexpr int total = S + RING * 8;     // 1324 elements
 };
 
 // ------------------------------------------------------------------ TMA input staging
@@ -238,17 +251,7 @@ __device__ __forceinline__ bool finite_(T v) {
 // stage record) and the defect b_k.  Stages are independent (multiple shooting) and nothing in the
 // model depends on the position, so column p_a of A_k is the constant e_a: only the 14 columns
 // u, v, q, w are integrated, one per lane, and the two half-warps take two stages at a time.
-// The position columns are written once per launch (init_position_columns).
-template <typename T>
-__device__ __forceinline__ void init_position_columns(int N, T* __restrict__ ws,
-                                                      const WsLayout& L, int lane) {
-  _Pragma("unroll 1") for (int idx = lane; idx < N * NX * 3; idx += 32) {
-    const int k = idx / (NX * 3), r = idx - k * (NX * 3);
-    const int i = r / 3, a = r - 3 * i;
-    ws[L.M + k * REC + i * M_LD + NU + a] = (i == a) ? T(1) : T(0);
-  }
-}
-
+// The v columns are integrated but not stored either (constant [dt I; I; 0; 0]).
 template <typename T, int NS, int NF>
 __device__ __forceinline__ void linearize(const DevCfg<T>& c, T* __restrict__ ws,
                                           const WsLayout& Lr, T* __restrict__ sm, int lane) {
@@ -271,9 +274,10 @@ __device__ __forceinline__ void linearize(const DevCfg<T>& c, T* __restrict__ ws
   T* M = ws + L.M;
   T* bv = ws + L.b;
   const int h = lane >> 4, cl = lane & 15;
-  const bool ccol = cl < NZ - 3;              // 14 integrated columns per stage
   const int sx = cl - 1;                      // state seeded by lanes 4..13: v, q, w = 3..12
-  const int zc = cl < NU ? cl : cl + 3;       // column of M_k = [B | A]
+  // stored columns: u (lanes 0..3) and q, w (lanes 7..13); lanes 4..6 carry the constant v columns
+  const bool ccol = cl < NU || (cl >= 7 && cl < 14);
+  const int zc = cl < NU ? cl : mcol_of_state(cl - 1 >= 6 ? cl - 1 : 6);  // column inside a row
   for (int k0 = 0; k0 < N; k0 += 2) {
     const bool live = k0 + h < N;           // odd horizons: the upper half idles on the last pass
     const int k = live ? k0 + h : N - 1;
@@ -296,10 +300,10 @@ __device__ __forceinline__ void linearize(const DevCfg<T>& c, T* __restrict__ ws
     T xl = x[0];  // every lane of a half holds the same nominal x; lane i writes component i
 #pragma unroll
     for (int i = 1; i < NX; i++) xl = (cl == i) ? x[i] : xl;
-    if (live && cl < NX) {  // defect; a copy rides in column 17 of M_k's rows (staged with the tile)
+    if (live && cl < NX) {  // defect; a copy rides in the last column of M_k's rows (staged with the tile)
       const T bk = xl - xb[(k + 1) * NX + cl];
       bv[k * NX + cl] = bk;
-      M[k * REC + cl * M_LD + NZ] = bk;
+      M[k * REC + cl * M_LD + MC_B] = bk;
     }
   }
 }

@@ -51,3 +51,6 @@ if 'all' in which or 'n20' in which:
 if 'all' in which or 'n600' in which:
     run('n600 rti', 1024, N=600)
     run('n600 rti', 148, N=600)
+if 'small' in which:
+    run('aggr rti', 1, hard=True)
+    run('aggr rti', 148, hard=True)
