@@ -43,6 +43,10 @@ extern "C" {
 #define NMPC_STATUS_MINSTEP 3
 #define NMPC_STATUS_QP_FAILURE 4
 
+#define NMPC_DISPATCH_AUTO 0
+#define NMPC_DISPATCH_FIFO 1
+#define NMPC_DISPATCH_LPT 2
+
 #define NMPC_PRECISION_F64 0
 #define NMPC_PRECISION_F32 1
 
@@ -69,7 +73,11 @@ typedef struct nmpc_config {
                               accepted iff it is primal feasible with non-negative multipliers (then
                               it IS the QP solution); otherwise the interior point runs as before.
                               0: interior point only.  RTI solves are not affected */
-  int32_t reserved0;       /* keeps the doubles 8-byte aligned; must be 0 */
+  int32_t dispatch;        /* order in which the problems of a batch are handed to the warps:
+                              NMPC_DISPATCH_AUTO (0): longest-expected-first when max_sqp_iter > 1 and
+                              the batch is larger than the number of resident warps, else by index;
+                              NMPC_DISPATCH_FIFO (1): by index; NMPC_DISPATCH_LPT (2): always sorted.
+                              Results do not depend on it (problems are independent) */
   double dt;
   double W[17];            /* stage weights [p(3) v(3) q(4) w(3) u(4)] (controller.py:234-240) */
   double We[13];           /* terminal weights (controller.py:241) */

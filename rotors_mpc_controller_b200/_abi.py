@@ -32,7 +32,7 @@ class NmpcConfig(C.Structure):
         ('N', C.c_int32), ('qp_iter_max', C.c_int32), ('integ_ns', C.c_int32),
         ('integ_steps', C.c_int32), ('cost_scale_dt', C.c_int32), ('lm_scaled_by_dt', C.c_int32),
         ('max_sqp_iter', C.c_int32), ('nan_status', C.c_int32), ('precision', C.c_int32),
-        ('ipm_warm_start', C.c_int32), ('active_set_shortcut', C.c_int32), ('reserved0', C.c_int32),
+        ('ipm_warm_start', C.c_int32), ('active_set_shortcut', C.c_int32), ('dispatch', C.c_int32),
         ('dt', C.c_double), ('W', C.c_double * 17), ('We', C.c_double * 13), ('lm', C.c_double),
         ('mass', C.c_double), ('J', C.c_double * 3), ('gravity', C.c_double),
         ('rotor_x', C.c_double * 4), ('rotor_y', C.c_double * 4), ('rotor_z', C.c_double * 4),

@@ -135,7 +135,10 @@ def abi_config(cp: ControllerParams, solver_cfg: Dict[str, object]) -> _abi.Nmpc
     c.nan_status = int(solver_cfg.get('nan_status', 4))
     c.ipm_warm_start = int(bool(solver_cfg.get('ipm_warm_start', True)))
     c.active_set_shortcut = int(bool(solver_cfg.get('active_set_shortcut', True)))
-    c.reserved0 = 0
+    disp = str(solver_cfg.get('dispatch', 'auto')).lower()
+    if disp not in ('auto', 'fifo', 'lpt'):
+        raise ValueError('dispatch must be "auto", "fifo" or "lpt"')
+    c.dispatch = {'auto': 0, 'fifo': 1, 'lpt': 2}[disp]
     prec = str(solver_cfg.get('precision', 'f64')).lower()
     if prec not in ('f64', 'f32'):
         raise ValueError('precision must be "f64" or "f32"')

@@ -56,10 +56,72 @@ __global__ void __maxnreg__(sizeof(T) == 4 ? NMPC_MAXNREG_F32 : NMPC_MAXNREG)
   // at a time instead of in a fixed stride
   for (;;) {
     int prob = 0;
-    if (lane == 0) prob = atomicAdd(work_counter, 1);
+    if (lane == 0) {
+      prob = atomicAdd(work_counter, 1);
+      if (A.order && prob < A.batch) prob = A.order[prob];
+    }
     prob = __shfl_sync(FULL, prob, 0);
     if (prob >= A.batch) break;
     solve_one<T, NS, NF>(A, L, ws, sm, prob, lane);
+  }
+}
+
+// Longest-expected-first dispatch.  The work of a problem (SQP iterations x factorisations per
+// QP) varies by an order of magnitude inside a batch, and a launch with only a few problems per
+// resident warp ends when its longest problem does: handing the long ones out FIRST shortens the
+// tail.  Nobody knows the iteration count in advance; the value of the problem's own objective at
+// the start (controller.py:223-245, state part:  N (x0 - yref_0)' W (x0 - yref_0) + (x0 - yref_e)'
+// W_e (x0 - yref_e), the cost of staying put over the horizon) ranks it well enough (Spearman 0.6 with the
+// factorisation count on configs[1]).  One CTA: keys -> 1024 logarithmic bins -> counting sort,
+// largest first; the order inside a bin is arbitrary (results do not depend on the order at all).
+constexpr int ORDER_BINS = 1024;
+template <typename T>
+__device__ __forceinline__ int order_bin(const DevCfg<T>& c, const double* __restrict__ x0,
+                                         const double* __restrict__ y0, const double* __restrict__ ye,
+                                         double nstages) {
+  double key = 0.0;
+#pragma unroll
+  for (int i = 0; i < NX; i++) {
+    const double xi = x0[i], e0 = xi - y0[i], e1 = xi - ye[i];
+    key += nstages * (double)c.Wq[i] * e0 * e0 + (double)c.We[i] * e1 * e1;
+  }
+  if (!(key == key) || key > 1e30) return ORDER_BINS - 1;   // NaN / inf inputs: anywhere
+  const int b = (int)(48.0 * log2(1.0 + 16.0 * key));       // ~2 % resolution over 6 decades
+  return b < 0 ? 0 : (b > ORDER_BINS - 1 ? ORDER_BINS - 1 : b);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(1024)
+    order_kernel(const __grid_constant__ DevCfg<T> c, int batch, int N, const double* __restrict__ x0,
+                 const double* __restrict__ yref, const double* __restrict__ yref_e,
+                 int* __restrict__ order) {
+  __shared__ int hist[ORDER_BINS];
+  const int t = threadIdx.x;
+  hist[t] = 0;
+  __syncthreads();
+  for (int p = t; p < batch; p += 1024)
+    atomicAdd(&hist[order_bin(c, x0 + (size_t)p * NX, yref + (size_t)p * N * NZ, yref_e + (size_t)p * NX,
+                              (double)N)], 1);
+  __syncthreads();
+  // exclusive prefix sum over the bins in DESCENDING key order: thread t owns bin 1023 - t
+  const int mine = hist[ORDER_BINS - 1 - t];
+  __syncthreads();
+  hist[t] = mine;
+  __syncthreads();
+  for (int off = 1; off < ORDER_BINS; off <<= 1) {
+    const int v = (t >= off) ? hist[t - off] : 0;
+    __syncthreads();
+    hist[t] += v;
+    __syncthreads();
+  }
+  const int excl = hist[t] - mine;
+  __syncthreads();
+  hist[t] = excl;   // start of descending bin t
+  __syncthreads();
+  for (int p = t; p < batch; p += 1024) {
+    const int b = order_bin(c, x0 + (size_t)p * NX, yref + (size_t)p * N * NZ, yref_e + (size_t)p * NX,
+                            (double)N);
+    order[atomicAdd(&hist[ORDER_BINS - 1 - b], 1)] = p;
   }
 }
 
@@ -208,6 +270,7 @@ struct nmpc_handle {
   double *xtraj, *utraj, *last_cmd;
   uint8_t* valid;
   int *qp_iters, *sqp_iters, *counter;
+  int* order;       // dispatch order of the batch (order_kernel)
   // staging for nmpc_solve_host
   double *s_x0, *s_yref, *s_yref_e, *s_u0, *s_thrust, *s_speed;
   int* s_status;
@@ -245,6 +308,7 @@ static int validate(const nmpc_config_t* c) {
   if (!(c->dt > 0.0)) return NMPC_E_INVALID;
   if (c->integ_ns != 1 && c->integ_ns != 2 && c->integ_ns != 4) return NMPC_E_INVALID;
   if (c->integ_steps < 1 || c->qp_iter_max < 1) return NMPC_E_INVALID;
+  if (c->dispatch < NMPC_DISPATCH_AUTO || c->dispatch > NMPC_DISPATCH_LPT) return NMPC_E_INVALID;
   if (c->precision != NMPC_PRECISION_F64 && c->precision != NMPC_PRECISION_F32)
     return NMPC_E_INVALID;
   if (!(c->mass > 0.0) || !(c->J[0] > 0.0) || !(c->J[1] > 0.0) || !(c->J[2] > 0.0))
@@ -339,6 +403,7 @@ static int create_impl(nmpc_handle* h, const nmpc_config_t* cfg, int batch, int 
   CK(cudaMalloc(&h->qp_iters, B * sizeof(int)));
   CK(cudaMalloc(&h->sqp_iters, B * sizeof(int)));
   CK(cudaMalloc(&h->counter, sizeof(int)));
+  CK(cudaMalloc(&h->order, B * sizeof(int)));
   CK(cudaMalloc(&h->s_x0, B * NX * sizeof(double)));
   CK(cudaMalloc(&h->s_yref, B * N * NZ * sizeof(double)));
   CK(cudaMalloc(&h->s_yref_e, B * NX * sizeof(double)));
@@ -396,6 +461,7 @@ int nmpc_destroy(nmpc_handle_t* h) {
   cudaFree(h->qp_iters);
   cudaFree(h->sqp_iters);
   cudaFree(h->counter);
+  cudaFree(h->order);
   cudaFree(h->s_x0);
   cudaFree(h->s_yref);
   cudaFree(h->s_yref_e);
@@ -514,6 +580,17 @@ static int launch_solve(nmpc_handle* h, const double* x0, const double* yref, co
   // one workspace per handle: a solve on another stream than the previous one queues behind it
   CK(cudaStreamWaitEvent(st, h->ev_last, 0));
   CK(cudaMemsetAsync(h->counter, 0, sizeof(int), st));
+  // longest-expected-first dispatch when the launch is a few waves of very unequal problems
+  const int disp = h->cfg.dispatch;
+  const bool lpt = disp == NMPC_DISPATCH_LPT ||
+                   (disp == NMPC_DISPATCH_AUTO && h->cfg.max_sqp_iter > 1 && h->batch > h->nslots);
+  A.order = nullptr;
+  if (lpt) {
+    order_kernel<T><<<1, 1024, 0, st>>>(A.cfg, h->batch, h->cfg.N, x0, yref, yref_e, h->order);
+    h->launches++;
+    CK(cudaGetLastError());
+    A.order = h->order;
+  }
   if (h->poison) CK(cudaMemsetAsync(h->ws, 0xff, h->ws_bytes, st));  // all-ones = NaN in FP64 / FP32
   nmpc_solve_kernel<T, NS, NF>
       <<<h->grid, WARPS * 32, smem, st>>>(A, h->L, h->counter);
