@@ -67,12 +67,13 @@ typedef struct nmpc_config {
   int32_t ipm_warm_start;  /* 1: inside one solve with max_sqp_iter > 1, QPs after the first start the
                               interior point from the previous QP's slacks / multipliers (see
                               NMPC_WARM_*); 0: every QP starts cold.  RTI solves are not affected */
-  int32_t active_set_shortcut; /* 1: inside one solve with max_sqp_iter > 1, a QP first tries the
-                              previous QP's active set: the equality-constrained problem with those
-                              inputs fixed on their bounds is solved exactly in ONE factorisation and
-                              accepted iff it is primal feasible with non-negative multipliers (then
-                              it IS the QP solution); otherwise the interior point runs as before.
-                              0: interior point only.  RTI solves are not affected */
+  int32_t active_set_shortcut; /* 1: every QP is first attacked by primal-dual active-set iterations:
+                              the equality-constrained problem with the inputs of the current set fixed
+                              on their bounds is solved exactly in ONE factorisation (the set starts
+                              from the previous QP's active set inside one solve, else empty) and the
+                              point is accepted iff it is primal and dual feasible -- then it IS the QP
+                              solution; otherwise the set is updated, at most NMPC_AS_MAXIT times, and
+                              finally the interior point takes over.  0: interior point only */
   int32_t dispatch;        /* order in which the problems of a batch are handed to the warps:
                               NMPC_DISPATCH_AUTO (0): longest-expected-first when max_sqp_iter > 1 and
                               the batch is larger than the number of resident warps, else by index;
@@ -105,6 +106,8 @@ typedef struct nmpc_config {
 #define NMPC_WARM_STEP_MAX 0.3
 #define NMPC_WARM_EPS_MIN 1e-8
 #define NMPC_WARM_EPS_MAX 0.1
+/* active-set iterations tried per QP before the interior point takes over */
+#define NMPC_AS_MAXIT 10
 
 typedef struct nmpc_handle nmpc_handle_t;
 

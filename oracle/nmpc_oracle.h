@@ -64,8 +64,9 @@ typedef struct {
   int nan_status;     /* status reported when NaNs appear (4 = QP failure, or 1) */
   int ipm_warm;       /* 1: QPs after the first of an SQP run (max_sqp_iter > 1) warm-start the
                          interior point from the previous QP's (t, lam), see ORC_WARM_* */
-  int as_shortcut;    /* 1: QPs after the first of an SQP run first try the previous QP's active set
-                         (orc_qp_solve_active_set, one factorisation) before the interior point */
+  int as_shortcut;    /* 1: every QP is first attacked by primal-dual active-set iterations
+                         (orc_qp_solve_active_set, one factorisation each, see orc_solve); the interior
+                         point is the fallback.  0: interior point only */
   int keep_state_box; /* 1: the +-state_box rows on all 13 states at stages 1..N-1
                          (controller.py:257-261) are real inequality rows of the QP, as in the
                          reference's HPIPM problem.  ORACLE-ONLY sensitivity flag (default 0): the
@@ -88,6 +89,10 @@ typedef struct {
 #endif
 #ifndef ORC_WARM_EPS_MAX
 #define ORC_WARM_EPS_MAX 0.1
+#endif
+/* active-set iterations tried per QP before the interior point takes over */
+#ifndef ORC_AS_MAXIT
+#define ORC_AS_MAXIT 10
 #endif
 
 /* continuous model, controller.py:267-355 */

@@ -62,15 +62,22 @@ int orc_solve(const orc_config *c, const double *x0, const double *yref, const d
     if (c->ipm_warm && !c->keep_state_box && have_ipm && prev_step <= ORC_WARM_STEP_MAX)
       weps = fmin(fmax(ORC_WARM_KAPPA * prev_step, ORC_WARM_EPS_MIN), ORC_WARM_EPS_MAX);
     int qs = -1;
-    /* Active-set shortcut: the previous QP of this solve left a converged (t, lam); if its active
-     * set is still the right one this QP is solved exactly by one factorisation. */
-    if (c->as_shortcut && !c->keep_state_box && have_ipm) {
+    /* Active-set method first (c->as_shortcut): primal-dual active-set iterations on the box rows.
+     * The starting set is the active set of the previous QP of this solve when it left a valid
+     * (t, lam), else the empty set (the first solve is then the equality-constrained "phase 0").
+     * Every iteration is ONE Riccati factorisation with the inputs of the set eliminated + roll-out
+     * (+ a costate sweep for the multipliers when the set is not empty).  A point that is primal
+     * feasible on the free rows with non-negative multipliers on the fixed ones IS the solution of
+     * the strictly convex QP and is accepted; otherwise violated free rows join the set, fixed rows
+     * with a negative multiplier leave it, and the solve is repeated -- at most ORC_AS_MAXIT times,
+     * then the interior point takes over with everything as the previous QP left it. */
+    if (c->as_shortcut && !c->keep_state_box) {
       int nact = 0;
       for (int i = 0; i < N * NU; i++) {
-        act[i] = (ll[i] > tl[i]) ? 1 : ((lu[i] > tu[i]) ? 2 : 0);
+        act[i] = !have_ipm ? 0 : ((ll[i] > tl[i]) ? 1 : ((lu[i] > tu[i]) ? 2 : 0));
         nact += act[i] != 0;
       }
-      if (nact > 0) {
+      for (int rep = 0; rep < ORC_AS_MAXIT && tot_qp < c->qp_iter_max; rep++) {
         tot_qp++;
         if (orc_qp_solve_active_set(qp, act, dx, du, ll2, lu2) == 0) {
           qs = ORC_SUCCESS;
@@ -80,10 +87,23 @@ int orc_solve(const orc_config *c, const double *x0, const double *yref, const d
             tl[i] = (act[i] == 1) ? 0.0 : du[i] - qp->lb[i];
             tu[i] = (act[i] == 2) ? 0.0 : qp->ub[i] - du[i];
           }
+          have_ipm = nact > 0; /* a valid (t, lam) with a non-empty active set for the next QP */
           n_as_ok++;
-        } else {
-          n_as_fail++;
+          break;
         }
+        n_as_fail++;
+        int changed = 0;
+        for (int i = 0; i < N * NU; i++) {
+          const int a0 = act[i];
+          if (a0 == 0 && du[i] < qp->lb[i]) act[i] = 1;
+          else if (a0 == 0 && du[i] > qp->ub[i]) act[i] = 2;
+          else if (a0 == 1 && !(ll2[i] >= 0.0)) act[i] = 0;
+          else if (a0 == 2 && !(lu2[i] >= 0.0)) act[i] = 0;
+          changed += act[i] != a0;
+        }
+        if (!changed) break; /* NaN data or a broken factorisation: let the interior point report it */
+        nact = 0;
+        for (int i = 0; i < N * NU; i++) nact += act[i] != 0;
       }
     }
     if (qs < 0)

@@ -646,58 +646,89 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
   return status;
 }
 
-// ------------------------------------------------------------------ K2': active-set shortcut
-// Between the QPs of one SQP run the active set settles long before the iterate does.  When the
-// previous QP of this solve left a converged interior-point iterate (or an accepted shortcut), its
-// active set  { i : lam_i > t_i }  is tried first: the inputs of that set are fixed on their bounds
-// of the NEW QP, the remaining equality-constrained problem is solved exactly by one Riccati
-// factorisation with those inputs eliminated (factor_sweep asmode) + roll-out, and a costate sweep
-// delivers the multipliers.  The point is accepted iff it is primal feasible on the free rows and
-// dual feasible on the fixed ones -- then it IS the solution of the strictly convex QP, exact to
-// round-off, for one factorisation instead of the 3-6 of a warm interior point.  Otherwise nothing
-// is committed (t, lam of the previous QP are untouched) and the interior point runs as before.
-// Returns true when accepted; *tried = 1 when a factorisation was spent.
+// ------------------------------------------------------------------ K2': active-set method
+// Primal-dual active-set iterations on the box rows, tried before the interior point
+// (solver.active_set_shortcut, default on).  The starting set is the active set { i : lam_i > t_i }
+// of the previous QP of this solve when it left a valid (t, lam) (have_set), else the empty set --
+// the first solve is then the equality-constrained "phase 0" solve.  Every iteration is ONE Riccati
+// factorisation with the inputs of the set eliminated (factor_sweep asmode) + the roll-out, and, when
+// the set is not empty, a costate sweep for the multipliers.  A point that is primal feasible on the
+// free rows and dual feasible on the fixed ones IS the solution of the strictly convex QP (exact to
+// round-off) and is accepted; otherwise violated free rows join the set, fixed rows with a negative
+// multiplier leave it, and the solve is repeated, at most NMPC_AS_MAXIT times.  Nothing is committed
+// before acceptance (t, lam of the previous QP are untouched), so the interior point can take over.
+// On configs[1] this replaces 51.7 interior-point factorisations per solve by 21.3, and the longest
+// problem of a batch needs 40 instead of 120.
+// Returns true when accepted; *tried = factorisations spent; *nact = the accepted set is not empty.
 template <typename T, int NF>
 __device__ __forceinline__ bool as_solve(const DevCfg<T>& c, T* __restrict__ ws,
                                          const WsLayout& Lr, T* __restrict__ sm, int lane,
-                                         int* tried) {
+                                         bool have_set, int* tried, bool* nact) {
   NMPC_FIXED(c)
   PROF_T0();
   const int nb = N * NU;
   const T nan = (T)__int_as_float(0x7fc00000);
   *tried = 0;
+  *nact = false;
   bool any = false;
   _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
-    const bool lo = ws[L.ll + i] > ws[L.tl + i];
-    const bool up = !lo && (ws[L.lu + i] > ws[L.tu + i]);
+    const bool lo = have_set && (ws[L.ll + i] > ws[L.tl + i]);
+    const bool up = have_set && !lo && (ws[L.lu + i] > ws[L.tu + i]);
     ws[L.dr + i] = lo ? ws[L.lb + i] : (up ? ws[L.ubd + i] : nan);   // fixed value (NaN: free)
     ws[L.dtl + i] = lo ? T(1) : (up ? T(2) : T(0));                  // row code
     ws[L.rt + i] = ws[L.r + i];                                       // plain input gradient
     any = any || lo || up;
   }
-  if (!__any_sync(FULL, any)) return false;  // nothing active: the phase-0 solve is the shortcut
-  __syncwarp();
-  *tried = 1;
-  PROF_ADD(PH_ELEM);
-  bool ok = factor_sweep<T, NF>(c, ws, L, sm, lane, T(1), true);
-  PROF_ADD(PH_FACTOR);
-  if (!ok) return false;
-  forward_sweep<T, NF>(c, ws, L, sm, lane, T(1), false, true, false, L.kff, L.dx, L.du);
-  PROF_ADD(PH_FWD);
-  ok = costate_check<T, NF>(c, ws, L, sm, lane);
-  PROF_ADD(PH_DELTA);
-  if (!ok) return false;
-  // accepted: slacks / multipliers of this point are the warm start and active set of the next QP
-  _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
-    const T code = ws[L.dtl + i], du = ws[L.du + i];
-    ws[L.tl + i] = code == T(1) ? T(0) : du - ws[L.lb + i];
-    ws[L.tu + i] = code == T(2) ? T(0) : ws[L.ubd + i] - du;
-    ws[L.ll + i] = ws[L.dll + i];
-    ws[L.lu + i] = ws[L.dlu + i];
+  any = __any_sync(FULL, any);
+  for (int rep = 0; rep < NMPC_AS_MAXIT; rep++) {
+    __syncwarp();
+    *tried += 1;
+    PROF_ADD(PH_ELEM);
+    bool ok = factor_sweep<T, NF>(c, ws, L, sm, lane, T(1), any);
+    PROF_ADD(PH_FACTOR);
+    if (!ok) return false;
+    forward_sweep<T, NF>(c, ws, L, sm, lane, T(1), false, true, false, L.kff, L.dx, L.du);
+    PROF_ADD(PH_FWD);
+    if (any) {
+      ok = costate_check<T, NF>(c, ws, L, sm, lane);
+      PROF_ADD(PH_DELTA);
+    } else {  // nothing fixed: the point is the solution iff it respects the box
+      _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
+        const T du = ws[L.du + i];
+        ok = ok && (du >= ws[L.lb + i]) && (du <= ws[L.ubd + i]);
+      }
+      ok = __all_sync(FULL, ok);
+    }
+    if (ok) {  // accepted: slacks / multipliers of this point are the active set and the warm start of the next QP
+      _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
+        const T code = ws[L.dtl + i], du = ws[L.du + i];
+        ws[L.tl + i] = code == T(1) ? T(0) : du - ws[L.lb + i];
+        ws[L.tu + i] = code == T(2) ? T(0) : ws[L.ubd + i] - du;
+        ws[L.ll + i] = any ? ws[L.dll + i] : T(0);
+        ws[L.lu + i] = any ? ws[L.dlu + i] : T(0);
+      }
+      __syncwarp();
+      *nact = any;
+      PROF_ADD(PH_ELEM);
+      return true;
+    }
+    // primal-dual update of the set
+    bool changed = false, any_new = false;
+    _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
+      const T code = ws[L.dtl + i], du = ws[L.du + i], lb = ws[L.lb + i], ub = ws[L.ubd + i];
+      T ncode = code;
+      if (code == T(0)) ncode = du < lb ? T(1) : (du > ub ? T(2) : T(0));
+      else if (any && code == T(1) && !(ws[L.dll + i] >= T(0))) ncode = T(0);
+      else if (any && code == T(2) && !(ws[L.dlu + i] >= T(0))) ncode = T(0);
+      changed = changed || (ncode != code);
+      any_new = any_new || (ncode != T(0));
+      ws[L.dtl + i] = ncode;
+      ws[L.dr + i] = ncode == T(1) ? lb : (ncode == T(2) ? ub : nan);
+    }
+    if (!__any_sync(FULL, changed)) return false;  // NaN data / no progress: the interior point reports it
+    any = __any_sync(FULL, any_new);
   }
-  __syncwarp();
-  PROF_ADD(PH_ELEM);
-  return true;
+  return false;
 }
 
 // ------------------------------------------------------------------ whole solve (K1+K2+K3)
@@ -837,9 +868,13 @@ __device__ __forceinline__ void solve_one(const SolveArgs<T>& A, const WsLayout&
     if (c.ipm_warm && have_ipm && prev_step <= T(NMPC_WARM_STEP_MAX))
       weps = fmin(fmax(T(NMPC_WARM_KAPPA) * prev_step, eps_min), T(NMPC_WARM_EPS_MAX));
     int qs = -1;
-    if (c.as_shortcut && have_ipm) {
+    if (c.as_shortcut) {
       int tried = 0;
-      if (as_solve<T, NF>(c, ws, L, sm, lane, &tried)) qs = ST_SUCCESS;
+      bool nact = false;
+      if (as_solve<T, NF>(c, ws, L, sm, lane, have_ipm, &tried, &nact)) {
+        qs = ST_SUCCESS;
+        have_ipm = nact;  // a valid (t, lam) with a non-empty active set for the next QP
+      }
       tot_qp += tried;
     }
     if (qs < 0) qs = ipm_solve<T, NF>(c, ws, L, sm, lane, weps, &have_ipm, &qi);
