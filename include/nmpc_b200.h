@@ -107,7 +107,7 @@ typedef struct nmpc_config {
 #define NMPC_WARM_EPS_MIN 1e-8
 #define NMPC_WARM_EPS_MAX 0.1
 /* active-set iterations tried per QP before the interior point takes over */
-#define NMPC_AS_MAXIT 10
+#define NMPC_AS_MAXIT 32
 
 typedef struct nmpc_handle nmpc_handle_t;
 

@@ -92,7 +92,7 @@ typedef struct {
 #endif
 /* active-set iterations tried per QP before the interior point takes over */
 #ifndef ORC_AS_MAXIT
-#define ORC_AS_MAXIT 10
+#define ORC_AS_MAXIT 32
 #endif
 
 /* continuous model, controller.py:267-355 */

@@ -52,17 +52,20 @@ __global__ void __maxnreg__(sizeof(T) == 4 ? NMPC_MAXNREG_F32 : NMPC_MAXNREG)
   }
   const int slot = blockIdx.x * WARPS + warp;
   T* ws = A.ws + (size_t)slot * L.total;
-  // dynamic work queue: iteration counts differ per problem, so problems are handed out one
-  // at a time instead of in a fixed stride
-  for (;;) {
-    int prob = 0;
-    if (lane == 0) {
-      prob = atomicAdd(work_counter, 1);
-      if (A.order && prob < A.batch) prob = A.order[prob];
+  // Work distribution.  First round: warp w of CTA b takes queue position w * gridDim.x + b, so a
+  // batch smaller than the number of resident warps spreads evenly over the SMs (and schedulers)
+  // instead of filling the first CTAs.  Afterwards a dynamic queue: iteration counts differ per
+  // problem, so problems are handed out one at a time instead of in a fixed stride.
+  int pos = warp * gridDim.x + blockIdx.x;
+  while (pos < A.batch) {
+    int prob = pos;
+    if (A.order) {
+      if (lane == 0) prob = A.order[pos];
+      prob = __shfl_sync(FULL, prob, 0);
     }
-    prob = __shfl_sync(FULL, prob, 0);
-    if (prob >= A.batch) break;
     solve_one<T, NS, NF>(A, L, ws, sm, prob, lane);
+    if (lane == 0) pos = atomicAdd(work_counter, 1) + gridDim.x * WARPS;
+    pos = __shfl_sync(FULL, pos, 0);
   }
 }
 
@@ -348,8 +351,7 @@ static int configure_kernel(nmpc_handle* h, size_t smem) {
     if (v >= 1 && v < occ) occ = v;
   }
   int grid = h->sm_count * occ;
-  const int need = (h->batch + WARPS - 1) / WARPS;
-  if (grid > need) grid = need;
+  if (grid > h->batch) grid = h->batch;   // small batches: one problem per CTA before a second warp is used
   h->grid = grid;
   h->nslots = grid * WARPS;
   return NMPC_OK;
