@@ -400,28 +400,55 @@ class PositionNMPC(BatchedPositionNMPC):
 
     def __init__(self, params: Dict[str, Dict[str, object]], device: int = 0) -> None:
         self._prev_solution_valid = False
+        self._io = None
         super().__init__(params, batch=1, device=device)
 
     def reconfigure(self, params: Dict[str, Dict[str, object]]) -> None:
         super().reconfigure(params)
         self._prev_solution_valid = False      # controller.py:167
+        self._io = None
 
     def solve(self, state: Dict[str, np.ndarray], reference: Dict[str, np.ndarray]
               ) -> Tuple[np.ndarray, int]:
-        """``(u0[4], status)``; ``u0`` is zeros when ``status != 0`` (controller.py:448-450)."""
-        position = np.asarray(state['position'], dtype=float).reshape(3)
-        velocity = np.asarray(state['velocity'], dtype=float).reshape(3)
+        """``(u0[4], status)``; ``u0`` is zeros when ``status != 0`` (controller.py:448-450).
+        Same marshalling as controller.py:401-445, written into preallocated buffers (this call is
+        the latency path: every numpy temporary costs as much as a Riccati stage)."""
+        N = self.horizon
+        buf = self._io
+        if buf is None or buf[1].shape[1] != N:
+            x0 = np.empty((1, 13))
+            yref = np.empty((1, N, 17))
+            yref_e = np.empty((1, 13))
+            out = (np.empty((1, 4)), np.empty((1,), np.int32), np.empty((1, 4)), np.empty((1, 4)))
+            ptrs = [_abi.ptr(a) for a in (x0, yref, yref_e) + out]
+            buf = self._io = (x0, yref, yref_e, out, ptrs)
+        x0, yref, yref_e, out, ptrs = buf
         quaternion = np.asarray(state['quaternion'], dtype=float).reshape(4)
-        body_rates = np.asarray(state['body_rates'], dtype=float).reshape(3)
         norm_q = np.linalg.norm(quaternion)
         if norm_q == 0.0:
             raise ValueError('Quaternion norm must be non-zero.')
-        x0 = np.concatenate((position, velocity, quaternion / norm_q, body_rates))
-        yref, yref_e = stack_reference(reference, self.horizon)
-        u0, status = super().solve(x0[None], yref[None], yref_e[None])
-        st = int(status[0])
+        x = x0[0]
+        x[0:3] = np.asarray(state['position'], dtype=float).reshape(3)
+        x[3:6] = np.asarray(state['velocity'], dtype=float).reshape(3)
+        x[6:10] = quaternion / norm_q
+        x[10:13] = np.asarray(state['body_rates'], dtype=float).reshape(3)
+        pos, vel = reference['positions'], reference['velocities']       # controller.py:433-445
+        quat, rate = reference['quaternions'], reference['body_rates']
+        y, ye = yref[0], yref_e[0]
+        y[:, 0:3] = pos[:N]
+        y[:, 3:6] = vel[:N]
+        y[:, 6:10] = quat[:N]
+        y[:, 10:13] = rate[:N]
+        y[:, 13:17] = reference['thrusts'][:N]
+        ye[0:3] = pos[-1]
+        ye[3:6] = vel[-1]
+        ye[6:10] = quat[-1]
+        ye[10:13] = rate[-1]
+        _abi.check(_abi.lib().nmpc_solve_host(self._h.ptr, *ptrs), 'nmpc_solve_host')
+        self._out = out
+        st = int(out[1][0])
         self._prev_solution_valid = (st == 0)
-        return (np.zeros(self.nu) if st != 0 else u0[0].copy()), st
+        return (np.zeros(self.nu) if st != 0 else out[0][0].copy()), st
 
     def command(self) -> Tuple[np.ndarray, np.ndarray]:
         thrust, speed = super().command()

@@ -32,6 +32,7 @@ namespace {
 #define NMPC_MAXNREG_F32 128
 #endif
 constexpr int WARPS = NMPC_WARPS;  // warps (= problems in flight) per CTA
+constexpr size_t SMALL_HOST_BYTES = 256 * 1024;  // nmpc_solve_host packs batches up to this input size
 
 constexpr int smem_elems_per_warp() { return smem_tile_elems(); }
 
@@ -274,7 +275,11 @@ struct nmpc_handle {
   uint8_t* valid;
   int *qp_iters, *sqp_iters, *counter;
   int* order;       // dispatch order of the batch (order_kernel)
-  // staging for nmpc_solve_host
+  // staging for nmpc_solve_host: ONE device allocation each for the inputs [x0 | yref | yref_e] and the
+  // outputs [u0 | thrust | speed | status] (sections padded to 16 bytes), so that a small batch moves
+  // with one H2D and one D2H copy through the pinned host mirrors pin_in / pin_out
+  unsigned char *s_in, *s_out, *pin_in, *pin_out;
+  size_t in_bytes, out_bytes, off_yref, off_yref_e, off_thrust, off_speed, off_status;
   double *s_x0, *s_yref, *s_yref_e, *s_u0, *s_thrust, *s_speed;
   int* s_status;
   uint8_t* s_mask;       // staging of a host mask (nmpc_invalidate)
@@ -406,13 +411,27 @@ static int create_impl(nmpc_handle* h, const nmpc_config_t* cfg, int batch, int 
   CK(cudaMalloc(&h->sqp_iters, B * sizeof(int)));
   CK(cudaMalloc(&h->counter, sizeof(int)));
   CK(cudaMalloc(&h->order, B * sizeof(int)));
-  CK(cudaMalloc(&h->s_x0, B * NX * sizeof(double)));
-  CK(cudaMalloc(&h->s_yref, B * N * NZ * sizeof(double)));
-  CK(cudaMalloc(&h->s_yref_e, B * NX * sizeof(double)));
-  CK(cudaMalloc(&h->s_u0, B * NU * sizeof(double)));
-  CK(cudaMalloc(&h->s_thrust, B * NU * sizeof(double)));
-  CK(cudaMalloc(&h->s_speed, B * NU * sizeof(double)));
-  CK(cudaMalloc(&h->s_status, B * sizeof(int)));
+  auto pad16 = [](size_t v) { return (v + 15) & ~(size_t)15; };
+  h->off_yref = pad16(B * NX * sizeof(double));
+  h->off_yref_e = h->off_yref + pad16(B * N * NZ * sizeof(double));
+  h->in_bytes = h->off_yref_e + pad16(B * NX * sizeof(double));
+  h->off_thrust = pad16(B * NU * sizeof(double));
+  h->off_speed = 2 * h->off_thrust;
+  h->off_status = 3 * h->off_thrust;
+  h->out_bytes = h->off_status + pad16(B * sizeof(int));
+  CK(cudaMalloc(&h->s_in, h->in_bytes));
+  CK(cudaMalloc(&h->s_out, h->out_bytes));
+  h->s_x0 = reinterpret_cast<double*>(h->s_in);
+  h->s_yref = reinterpret_cast<double*>(h->s_in + h->off_yref);
+  h->s_yref_e = reinterpret_cast<double*>(h->s_in + h->off_yref_e);
+  h->s_u0 = reinterpret_cast<double*>(h->s_out);
+  h->s_thrust = reinterpret_cast<double*>(h->s_out + h->off_thrust);
+  h->s_speed = reinterpret_cast<double*>(h->s_out + h->off_speed);
+  h->s_status = reinterpret_cast<int*>(h->s_out + h->off_status);
+  if (h->in_bytes <= SMALL_HOST_BYTES) {  // latency path of nmpc_solve_host (e.g. the single vehicle)
+    CK(cudaHostAlloc(&h->pin_in, h->in_bytes, cudaHostAllocDefault));
+    CK(cudaHostAlloc(&h->pin_out, h->out_bytes, cudaHostAllocDefault));
+  }
   CK(cudaMalloc(&h->s_mask, B));
   cudaStream_t st = h->stream;
   CK(cudaMemsetAsync(h->ws, 0, h->ws_bytes, st));
@@ -464,13 +483,10 @@ int nmpc_destroy(nmpc_handle_t* h) {
   cudaFree(h->sqp_iters);
   cudaFree(h->counter);
   cudaFree(h->order);
-  cudaFree(h->s_x0);
-  cudaFree(h->s_yref);
-  cudaFree(h->s_yref_e);
-  cudaFree(h->s_u0);
-  cudaFree(h->s_thrust);
-  cudaFree(h->s_speed);
-  cudaFree(h->s_status);
+  cudaFree(h->s_in);
+  cudaFree(h->s_out);
+  if (h->pin_in) cudaFreeHost(h->pin_in);
+  if (h->pin_out) cudaFreeHost(h->pin_out);
   cudaFree(h->s_mask);
   if (h->ev_last) cudaEventDestroy(h->ev_last);
   if (h->stream) cudaStreamDestroy(h->stream);
@@ -633,6 +649,24 @@ int nmpc_solve_host(nmpc_handle_t* h, const double* x0, const double* yref, cons
   CK(cudaSetDevice(h->device));
   const size_t B = h->batch, N = h->cfg.N;
   cudaStream_t st = h->stream;
+  if (h->pin_in) {
+    // small batch: pack into the pinned mirror, ONE H2D copy, solve, ONE D2H copy (7 copies of
+    // pageable memory cost more than the solve of a single vehicle)
+    memcpy(h->pin_in, x0, B * NX * sizeof(double));
+    memcpy(h->pin_in + h->off_yref, yref, B * N * NZ * sizeof(double));
+    memcpy(h->pin_in + h->off_yref_e, yref_e, B * NX * sizeof(double));
+    CK(cudaMemcpyAsync(h->s_in, h->pin_in, h->in_bytes, cudaMemcpyHostToDevice, st));
+    int rc = nmpc_solve_device(h, h->s_x0, h->s_yref, h->s_yref_e, h->s_u0, h->s_status, h->s_thrust,
+                               h->s_speed, st);
+    if (rc != NMPC_OK) return rc;
+    CK(cudaMemcpyAsync(h->pin_out, h->s_out, h->out_bytes, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (u0) memcpy(u0, h->pin_out, B * NU * sizeof(double));
+    if (thrust) memcpy(thrust, h->pin_out + h->off_thrust, B * NU * sizeof(double));
+    if (speed) memcpy(speed, h->pin_out + h->off_speed, B * NU * sizeof(double));
+    if (status) memcpy(status, h->pin_out + h->off_status, B * sizeof(int));
+    return NMPC_OK;
+  }
   CK(cudaMemcpyAsync(h->s_x0, x0, B * NX * sizeof(double), cudaMemcpyHostToDevice, st));
   CK(cudaMemcpyAsync(h->s_yref, yref, B * N * NZ * sizeof(double), cudaMemcpyHostToDevice, st));
   CK(cudaMemcpyAsync(h->s_yref_e, yref_e, B * NX * sizeof(double), cudaMemcpyHostToDevice, st));
