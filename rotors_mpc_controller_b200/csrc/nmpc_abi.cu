@@ -22,16 +22,13 @@ namespace {
 // to 170 registers, 4 per scheduler need <= 128 (FP32 kernels do, FP64 ones spill in the sweeps and
 // lose more than the extra warps bring).  The FP64 cap is set a little below what ptxas would take
 // (156): the 160-register schedule measures 4-5 % faster than the unconstrained one.
-#ifndef NMPC_WARPS
-#define NMPC_WARPS 4
-#endif
 #ifndef NMPC_MAXNREG
 #define NMPC_MAXNREG 160
 #endif
 #ifndef NMPC_MAXNREG_F32
 #define NMPC_MAXNREG_F32 128
 #endif
-constexpr int WARPS = NMPC_WARPS;  // warps (= problems in flight) per CTA
+constexpr int WARPS = CTA_WARPS;  // warps (= problems in flight) per CTA
 constexpr size_t SMALL_HOST_BYTES = 256 * 1024;  // nmpc_solve_host packs batches up to this input size
 
 constexpr int smem_elems_per_warp() { return smem_tile_elems(); }
@@ -50,6 +47,14 @@ __global__ void __maxnreg__(sizeof(T) == 4 ? NMPC_MAXNREG_F32 : NMPC_MAXNREG)
   if (A.stage && lane == 0) {  // mbarrier of the TMA input staging + its phase parity
     reinterpret_cast<unsigned*>(sm + SmemLayout::bar)[2] = 0u;
     mbar_init(sm + SmemLayout::bar);
+  }
+  {  // constants shared by the CTA (see VBLOCK_ELEMS)
+    T* vblock = reinterpret_cast<T*>(smem_raw) + WARPS * smem_elems_per_warp();
+    for (int e = threadIdx.x; e < VBLOCK_ELEMS; e += blockDim.x) {
+      const int i = e / M_LD, a = e - i * M_LD;
+      vblock[e] = (a < 3) ? ((i == a) ? A.cfg.dt : ((i == 3 + a) ? T(1) : T(0))) : T(0);
+    }
+    __syncthreads();  // the only CTA-wide barrier: afterwards the warps run independently
   }
   const int slot = blockIdx.x * WARPS + warp;
   T* ws = A.ws + (size_t)slot * L.total;
@@ -364,7 +369,7 @@ static int configure_kernel(nmpc_handle* h, size_t smem) {
 
 template <typename T>
 static size_t solve_smem_bytes(const nmpc_handle* h) {
-  return (size_t)WARPS * smem_elems_per_warp() * sizeof(T);
+  return ((size_t)WARPS * smem_elems_per_warp() + VBLOCK_ELEMS) * sizeof(T);
 }
 
 template <typename T>

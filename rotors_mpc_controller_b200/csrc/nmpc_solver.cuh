@@ -172,6 +172,13 @@ __host__ __device__ inline StageLayout make_stage_layout(int N, int elem_bytes) 
   return S;
 }
 constexpr int smem_tile_elems() { return (SmemLayout::total + 3) & ~3; }  // per-warp tile of T
+// CTAs of CTA_WARPS independent warps; behind their tiles one block of constants shared by the CTA:
+// VBLOCK = the v columns of every A_k, dt e_{p_a} + e_{v_a}, as columns 0..2 of a 13 x M_LD block
+#ifndef NMPC_WARPS
+#define NMPC_WARPS 4
+#endif
+constexpr int CTA_WARPS = NMPC_WARPS;
+constexpr int VBLOCK_ELEMS = NX * M_LD;
 __device__ __forceinline__ unsigned smem_u32(const void* p) {
   return (unsigned)__cvta_generic_to_shared(p);
 }
