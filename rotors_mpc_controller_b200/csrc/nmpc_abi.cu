@@ -81,8 +81,8 @@ __global__ void __maxnreg__(sizeof(T) == 4 ? NMPC_MAXNREG_F32 : NMPC_MAXNREG)
 // tail.  Nobody knows the iteration count in advance; the value of the problem's own objective at
 // the start (controller.py:223-245, state part:  N (x0 - yref_0)' W (x0 - yref_0) + (x0 - yref_e)'
 // W_e (x0 - yref_e), the cost of staying put over the horizon) ranks it well enough (Spearman 0.6 with the
-// factorisation count on configs[1]).  One CTA: keys -> 1024 logarithmic bins -> counting sort,
-// largest first; the order inside a bin is arbitrary (results do not depend on the order at all).
+// factorisation count on configs[1]).  Keys -> 1024 logarithmic bins (whole grid) -> counting sort in
+// one CTA, largest first; the order inside a bin is arbitrary (results do not depend on the order).
 constexpr int ORDER_BINS = 1024;
 template <typename T>
 __device__ __forceinline__ int order_bin(const DevCfg<T>& c, const double* __restrict__ x0,
@@ -99,39 +99,41 @@ __device__ __forceinline__ int order_bin(const DevCfg<T>& c, const double* __res
   return b < 0 ? 0 : (b > ORDER_BINS - 1 ? ORDER_BINS - 1 : b);
 }
 
+// pass 1 (whole grid): bin of every problem + global histogram
 template <typename T>
+__global__ void __launch_bounds__(256)
+    order_bins_kernel(const __grid_constant__ DevCfg<T> c, int batch, int N, const double* __restrict__ x0,
+                      const double* __restrict__ yref, const double* __restrict__ yref_e,
+                      int* __restrict__ bins, int* __restrict__ hist) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= batch) return;
+  const int b = order_bin(c, x0 + (size_t)p * NX, yref + (size_t)p * N * NZ, yref_e + (size_t)p * NX,
+                          (double)N);
+  bins[p] = b;
+  atomicAdd(&hist[b], 1);
+}
+
+// pass 2 (one CTA): exclusive prefix sum over the bins in DESCENDING key order, then the scatter
 __global__ void __launch_bounds__(1024)
-    order_kernel(const __grid_constant__ DevCfg<T> c, int batch, int N, const double* __restrict__ x0,
-                 const double* __restrict__ yref, const double* __restrict__ yref_e,
-                 int* __restrict__ order) {
-  __shared__ int hist[ORDER_BINS];
+    order_scatter_kernel(int batch, const int* __restrict__ bins, int* __restrict__ hist,
+                         int* __restrict__ order) {
+  __shared__ int start[ORDER_BINS];
   const int t = threadIdx.x;
-  hist[t] = 0;
-  __syncthreads();
-  for (int p = t; p < batch; p += 1024)
-    atomicAdd(&hist[order_bin(c, x0 + (size_t)p * NX, yref + (size_t)p * N * NZ, yref_e + (size_t)p * NX,
-                              (double)N)], 1);
-  __syncthreads();
-  // exclusive prefix sum over the bins in DESCENDING key order: thread t owns bin 1023 - t
-  const int mine = hist[ORDER_BINS - 1 - t];
-  __syncthreads();
-  hist[t] = mine;
+  const int mine = hist[ORDER_BINS - 1 - t];   // thread t owns bin 1023 - t
+  hist[ORDER_BINS - 1 - t] = 0;                // ready for the next launch
+  start[t] = mine;
   __syncthreads();
   for (int off = 1; off < ORDER_BINS; off <<= 1) {
-    const int v = (t >= off) ? hist[t - off] : 0;
+    const int v = (t >= off) ? start[t - off] : 0;
     __syncthreads();
-    hist[t] += v;
+    start[t] += v;
     __syncthreads();
   }
-  const int excl = hist[t] - mine;
+  const int excl = start[t] - mine;
   __syncthreads();
-  hist[t] = excl;   // start of descending bin t
+  start[t] = excl;
   __syncthreads();
-  for (int p = t; p < batch; p += 1024) {
-    const int b = order_bin(c, x0 + (size_t)p * NX, yref + (size_t)p * N * NZ, yref_e + (size_t)p * NX,
-                            (double)N);
-    order[atomicAdd(&hist[ORDER_BINS - 1 - b], 1)] = p;
-  }
+  for (int p = t; p < batch; p += 1024) order[atomicAdd(&start[ORDER_BINS - 1 - bins[p]], 1)] = p;
 }
 
 // Test hook: discretise n independent (x,u) pairs, one warp each.
@@ -279,7 +281,7 @@ struct nmpc_handle {
   double *xtraj, *utraj, *last_cmd;
   uint8_t* valid;
   int *qp_iters, *sqp_iters, *counter;
-  int* order;       // dispatch order of the batch (order_kernel)
+  int *order, *bins, *hist;   // dispatch order of the batch, work-key bins, their histogram (order_*_kernel)
   // staging for nmpc_solve_host: ONE device allocation each for the inputs [x0 | yref | yref_e] and the
   // outputs [u0 | thrust | speed | status] (sections padded to 16 bytes), so that a small batch moves
   // with one H2D and one D2H copy through the pinned host mirrors pin_in / pin_out
@@ -416,6 +418,8 @@ static int create_impl(nmpc_handle* h, const nmpc_config_t* cfg, int batch, int 
   CK(cudaMalloc(&h->sqp_iters, B * sizeof(int)));
   CK(cudaMalloc(&h->counter, sizeof(int)));
   CK(cudaMalloc(&h->order, B * sizeof(int)));
+  CK(cudaMalloc(&h->bins, B * sizeof(int)));
+  CK(cudaMalloc(&h->hist, ORDER_BINS * sizeof(int)));
   auto pad16 = [](size_t v) { return (v + 15) & ~(size_t)15; };
   h->off_yref = pad16(B * NX * sizeof(double));
   h->off_yref_e = h->off_yref + pad16(B * N * NZ * sizeof(double));
@@ -445,6 +449,7 @@ static int create_impl(nmpc_handle* h, const nmpc_config_t* cfg, int batch, int 
   CK(cudaMemsetAsync(h->valid, 0, B, st));
   CK(cudaMemsetAsync(h->qp_iters, 0, B * sizeof(int), st));
   CK(cudaMemsetAsync(h->sqp_iters, 0, B * sizeof(int), st));
+  CK(cudaMemsetAsync(h->hist, 0, ORDER_BINS * sizeof(int), st));
   CK(cudaEventRecord(h->ev_last, st));
   return nmpc_reset_last_command(h);
 }
@@ -488,6 +493,8 @@ int nmpc_destroy(nmpc_handle_t* h) {
   cudaFree(h->sqp_iters);
   cudaFree(h->counter);
   cudaFree(h->order);
+  cudaFree(h->bins);
+  cudaFree(h->hist);
   cudaFree(h->s_in);
   cudaFree(h->s_out);
   if (h->pin_in) cudaFreeHost(h->pin_in);
@@ -609,8 +616,10 @@ static int launch_solve(nmpc_handle* h, const double* x0, const double* yref, co
                    (disp == NMPC_DISPATCH_AUTO && h->cfg.max_sqp_iter > 1 && h->batch > h->nslots);
   A.order = nullptr;
   if (lpt) {
-    order_kernel<T><<<1, 1024, 0, st>>>(A.cfg, h->batch, h->cfg.N, x0, yref, yref_e, h->order);
-    h->launches++;
+    order_bins_kernel<T><<<(h->batch + 255) / 256, 256, 0, st>>>(A.cfg, h->batch, h->cfg.N, x0, yref,
+                                                                 yref_e, h->bins, h->hist);
+    order_scatter_kernel<<<1, 1024, 0, st>>>(h->batch, h->bins, h->hist, h->order);
+    h->launches += 2;
     CK(cudaGetLastError());
     A.order = h->order;
   }

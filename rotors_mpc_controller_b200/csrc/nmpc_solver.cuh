@@ -757,7 +757,7 @@ struct SolveArgs {
   int* qp_iters;
   int* sqp_iters;
   T* ws;                 // nslots * layout.total
-  const int* order;      // dispatch order (longest-expected-first, see order_kernel) or null: by index
+  const int* order;      // dispatch order (longest-expected-first, see order_bins_kernel) or null: by index
   int stage;             // 1: inputs staged by TMA bulk copies (make_stage_layout), 0: direct loads
   int poison;            // debug (nmpc_debug_poison): the shared tile is filled with NaN before every
                          // problem (and the host fills the workspace with NaN before every launch):

@@ -21,7 +21,9 @@ for rep in range(3):
     print(f'N=600 B={B} cold RTI rep {rep}: {e0.elapsed_time(e1):.2f} ms, {B/e0.elapsed_time(e1)*1e3:.0f} solves/s, '
           f'factorisations mean {it.mean():.2f} max {it.max()}, status {np.bincount(st.cpu().numpy())}, '
           f'workspace {ctl.workspace_bytes/2**20:.0f} MiB')
-ob = O.OracleBatch(O.config_from_params(params), 16)
-ur, sr, _, _ = ob.solve(x0[:16], yref[:16], yref_e[:16])
-print('oracle check (16 problems): status equal', np.array_equal(st.cpu().numpy()[:16], sr),
-      'max |u0 - oracle|', np.abs(u0.cpu().numpy()[:16] - ur).max())
+from tests import agreement as A
+o = A.oracle_parallel(params, {}, x0, yref, yref_e)
+stn, u0n = st.cpu().numpy(), u0.cpu().numpy()
+print('oracle check (all', B, 'problems): status equal', np.array_equal(stn, o['status']),
+      'factorisations equal', np.array_equal(ctl.stats()['qp_iters'], o['qp_iters']),
+      'max |u0 - oracle|', np.abs(u0n - o['u0']).max())
