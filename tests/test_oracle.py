@@ -167,6 +167,71 @@ def test_qp_against_independent_active_set(O, cfg, cold):
     assert nact_total > 100
 
 
+def test_active_set_solve_is_the_exact_kkt_solution(O, cfg):
+    """orc_qp_solve_active_set (one Riccati factorisation with the fixed inputs eliminated + costate
+    sweep) against the dense KKT solve of oracle/qp_check.py for the SAME active set: primal point,
+    multipliers and the accept / reject decision."""
+    import ctypes as C
+    from oracle import qp_check as Q
+    rng = np.random.default_rng(11)
+    L = O.lib()
+    n_acc = 0
+    for qp in _qp_cases(O, cfg, rng, 10, cold=False):
+        N = qp['A'].shape[0]
+        s = O.qp_solve(qp)
+        act_l = s['lam_l'] > (s['du'] - qp['lb'])
+        act_u = s['lam_u'] > (qp['ub'] - s['du'])
+        for flip in (False, True):     # the optimal set, and a perturbed (wrong) one
+            al, au = act_l.copy(), act_u.copy()
+            if flip:
+                al[0, 0], au[0, 0] = not al[0, 0], False
+            act = (al * 1 + au * 2).astype(np.uint8).reshape(-1)
+            c_qp = O.OrcQP()
+            c_qp.N = N
+            keep = {k: np.ascontiguousarray(qp[k], float) for k in ('A', 'B', 'b', 'Q', 'R', 'q', 'r', 'lb', 'ub')}
+            for k, a in keep.items():
+                setattr(c_qp, k, O._p(a))
+            dx, du = np.zeros((N + 1, 13)), np.zeros((N, 4))
+            ll, lu = np.zeros((N, 4)), np.zeros((N, 4))
+            L.orc_qp_solve_active_set.restype = C.c_int
+            rej = L.orc_qp_solve_active_set(C.byref(c_qp), act.ctypes.data_as(C.POINTER(C.c_ubyte)),
+                                            O._p(dx), O._p(du), O._p(ll), O._p(lu))
+            dxk, duk, llk, luk = Q.active_set_kkt(qp, al, au)
+            assert np.max(np.abs(du - duk)) < 1e-10 and np.max(np.abs(dx - dxk)) < 1e-10
+            assert np.max(np.abs(ll - llk)) < 1e-9 and np.max(np.abs(lu - luk)) < 1e-9
+            feasible = (np.all(duk >= qp['lb'] - 1e-13) and np.all(duk <= qp['ub'] + 1e-13)
+                        and llk[al].min(initial=1.0) > -1e-13 and luk[au].min(initial=1.0) > -1e-13)
+            assert (rej == 0) == feasible
+            n_acc += rej == 0
+    assert n_acc >= 10          # every optimal set is accepted (the perturbed ones mostly not)
+
+
+@pytest.mark.parametrize('kind', ['cfg2_sqp', 'aggressive_rti'])
+def test_active_set_method_matches_interior_point(O, params, kind):
+    """as_shortcut on / off in the oracle: same statuses, same SQP iteration behaviour, u0 within the
+    interior point's own accuracy, far fewer factorisations (the strictly convex QP has ONE solution,
+    whichever method finds it)."""
+    B, N = 96, 20
+    rng = np.random.default_rng(12)
+    hover = params['vehicle']['mass'] * 9.81 / 4
+    if kind == 'cfg2_sqp':
+        x0 = random_states(rng, B)
+        yref, yref_e = setpoint_refs(rng, x0, N, hover)
+        flags = dict(max_sqp_iter=50, sqp_tol=1e-8)
+    else:
+        x0, yref, yref_e = aggressive(rng, B, N, hover)
+        flags = {}
+    out = {}
+    for on in (0, 1):
+        ob = O.OracleBatch(O.config_from_params(params, as_shortcut=on, **flags), B)
+        u0, st, _, _ = ob.solve(x0, yref, yref_e)
+        out[on] = (u0, st, ob.qp_iters.copy())
+    assert np.array_equal(out[0][1], out[1][1]) and (out[1][1] == 0).all()
+    assert np.max(np.abs(out[0][0] - out[1][0])) < 5e-9
+    assert out[1][2].sum() < 0.6 * out[0][2].sum()
+    assert out[1][2].max() <= out[0][2].max()
+
+
 def test_unconstrained_qp_is_one_factorisation(O, cfg):
     from oracle import qp_check as Q
     rng = np.random.default_rng(6)
