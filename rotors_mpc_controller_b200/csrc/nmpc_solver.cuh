@@ -261,7 +261,9 @@ __device__ __forceinline__ bool finite_(T v) {
 // The v columns are integrated but not stored either (constant [dt I; I; 0; 0]).
 template <typename T, int NS, int NF>
 __device__ __forceinline__ void linearize(const DevCfg<T>& c, T* __restrict__ ws,
-                                          const WsLayout& Lr, T* __restrict__ sm, int lane) {
+                                          const WsLayout& Lr, T* __restrict__ sm, int lane,
+                                          const double* __restrict__ yref,
+                                          const double* __restrict__ yref_e, bool grads) {
   NMPC_FIXED(c)
   // The iterate is read stage by stage below (17 broadcast loads per pass, each pass would wait
   // for L2): when it fits the (idle) stage buffers it is copied to shared memory once, with all
@@ -299,6 +301,18 @@ __device__ __forceinline__ void linearize(const DevCfg<T>& c, T* __restrict__ ws
       u[i] = ub[k * NU + i];
       su[i] = (cl == i) ? T(1) : T(0);
     }
+    if (grads && live) {
+      // LINEAR_LS gradients and the delta-form box of this stage (what gradients() computes), in
+      // the same pass: the stage's reference row is read while the integrator runs
+      if (cl < NX) ws[L.q + k * NX + cl] = c.Wq[cl] * (xb[k * NX + cl] - (T)yref[k * NZ + cl]);
+      if (cl < NU) {
+        const T uu = ub[k * NU + cl];
+        ws[L.r + k * NU + cl] = c.Wr[cl] * (uu - (T)yref[k * NZ + NX + cl]);
+        ws[L.lb + k * NU + cl] = c.lbu[cl] - uu;
+        ws[L.ubd + k * NU + cl] = c.ubu[cl] - uu;
+        ws[L.Rt + k * NU + cl] = c.Rd[cl];
+      }
+    }
     erk_column<T, NS>(c, x, u, s, su);
     if (live && ccol) {
 #pragma unroll
@@ -313,6 +327,7 @@ __device__ __forceinline__ void linearize(const DevCfg<T>& c, T* __restrict__ ws
       M[k * REC + cl * M_LD + MC_B] = bk;
     }
   }
+  if (grads && lane < NX) ws[L.q + N * NX + lane] = c.We[lane] * (xb[N * NX + lane] - (T)yref_e[lane]);
 }
 
 // LINEAR_LS gradients (controller.py:223-245, stage cost scaled by dt) and the delta-form box.
@@ -865,9 +880,9 @@ __device__ __forceinline__ void solve_one(const SolveArgs<T>& A, const WsLayout&
   const T eps_min = sizeof(T) == 4 ? T(1e-4) : T(NMPC_WARM_EPS_MIN);
   const int max_sqp = c.max_sqp_iter < 1 ? 1 : c.max_sqp_iter;
   while (nsqp < max_sqp) {
-    linearize<T, NS, NF>(c, ws, L, sm, lane);
+    // (gradients of the first iteration: done by load_inputs from the TMA-staged references)
+    linearize<T, NS, NF>(c, ws, L, sm, lane, yref, yref_e, nsqp > 0);
     PROF_ADD(PH_LIN);
-    if (nsqp > 0) gradients<T, NF>(c, ws, L, yref, yref_e, lane);  // first iteration: done by load_inputs
     __syncwarp();
     PROF_ADD(PH_GRAD);
     int qi = 0;
