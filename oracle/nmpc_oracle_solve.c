@@ -77,7 +77,7 @@ int orc_solve(const orc_config *c, const double *x0, const double *yref, const d
         act[i] = !have_ipm ? 0 : ((ll[i] > tl[i]) ? 1 : ((lu[i] > tu[i]) ? 2 : 0));
         nact += act[i] != 0;
       }
-      for (int rep = 0; rep < ORC_AS_MAXIT && tot_qp < c->qp_iter_max; rep++) {
+      for (int rep = 0; rep < ORC_AS_MAXIT && rep < c->qp_iter_max; rep++) { /* iter_max caps every QP method */
         tot_qp++;
         if (orc_qp_solve_active_set(qp, act, dx, du, ll2, lu2) == 0) {
           qs = ORC_SUCCESS;

@@ -702,7 +702,7 @@ __device__ __forceinline__ bool as_solve(const DevCfg<T>& c, T* __restrict__ ws,
     any = any || lo || up;
   }
   any = __any_sync(FULL, any);
-  for (int rep = 0; rep < NMPC_AS_MAXIT; rep++) {
+  for (int rep = 0; rep < NMPC_AS_MAXIT && rep < c.qp_iter_max; rep++) {  // iter_max caps every QP method
     __syncwarp();
     *tried += 1;
     PROF_ADD(PH_ELEM);
