@@ -274,7 +274,8 @@ __device__ __forceinline__ void linearize(const DevCfg<T>& c, T* __restrict__ ws
   const T* ub = ws + L.ub;
   if (staged) {
     T* sx = sm + SmemLayout::M;
-    _Pragma("unroll 3") for (int i = lane; i < nxv; i += 32) sx[i] = xb[i];
+    // (fixed horizon: fully unrolled, all twelve loads of a lane in flight together)
+    _Pragma("unroll 9") for (int i = lane; i < nxv; i += 32) sx[i] = xb[i];
     _Pragma("unroll 3") for (int i = lane; i < nuv; i += 32) sx[nxv + i] = ub[i];
     xb = sx;
     ub = sx + nxv;
