@@ -254,11 +254,11 @@ __device__ __forceinline__ bool finite_(T v) {
 }
 
 // ------------------------------------------------------------------ K1: linearisation
-// For every stage: ERK + forward sensitivities -> M_k = [B_k | A_k] (row-major 13 x 18 in the
-// stage record) and the defect b_k.  Stages are independent (multiple shooting) and nothing in the
-// model depends on the position, so column p_a of A_k is the constant e_a: only the 14 columns
-// u, v, q, w are integrated, one per lane, and the two half-warps take two stages at a time.
-// The v columns are integrated but not stored either (constant [dt I; I; 0; 0]).
+// For every stage: ERK + forward sensitivities -> the stored columns of M_k = [B_k | A_k] (rows of
+// 12 in the stage record) and the defect b_k.  Stages are independent (multiple shooting) and
+// nothing in the model depends on the position or the velocity, so the p and v columns of A_k are
+// constants that are never formed: 11 columns (u, q, w) per stage are integrated, one per lane,
+// as directional derivatives of the ERK map (no Jacobian matrix is built).
 template <typename T, int NS, int NF>
 __device__ __forceinline__ void linearize(const DevCfg<T>& c, T* __restrict__ ws,
                                           const WsLayout& Lr, T* __restrict__ sm, int lane,
@@ -283,49 +283,57 @@ __device__ __forceinline__ void linearize(const DevCfg<T>& c, T* __restrict__ ws
   }
   T* M = ws + L.M;
   T* bv = ws + L.b;
-  const int h = lane >> 4, cl = lane & 15;
-  const int sx = cl - 1;                      // state seeded by lanes 4..13: v, q, w = 3..12
-  // stored columns: u (lanes 0..3) and q, w (lanes 7..13); lanes 4..6 carry the constant v columns
-  const bool ccol = cl < NU || (cl >= 7 && cl < 14);
-  const int zc = cl < NU ? cl : mcol_of_state(cl - 1 >= 6 ? cl - 1 : 6);  // column inside a row
-  for (int k0 = 0; k0 < N; k0 += 2) {
-    const bool live = k0 + h < N;           // odd horizons: the upper half idles on the last pass
-    const int k = live ? k0 + h : N - 1;
+  // The 11 stored columns of every stage (u0..u3, q0..q3, w0..w2 = columns 0..10 of a record row) are
+  // dealt out flat over the lanes: item = 11 * stage + column, 32 items per pass, so N = 20 takes
+  // 7 passes with every lane busy (a half-warp per stage with its 14 "computed" columns took 10).
+  constexpr int NCOL = NZ - 6;
+  const int total = N * NCOL;
+  for (int base = 0; base < total; base += 32) {
+    const bool live = base + lane < total;
+    const int item = live ? base + lane : total - 1;
+    const int k = item / NCOL, j = item - NCOL * k;
     T x[NX], u[NU], s[NX], su[NU];
 #pragma unroll
     for (int i = 0; i < NX; i++) {
       x[i] = xb[k * NX + i];
-      s[i] = (cl >= NU && sx == i) ? T(1) : T(0);
+      s[i] = (j >= NU && i == j + 2) ? T(1) : T(0);   // column j >= 4 is state j + 2 (q, w = 6..12)
     }
 #pragma unroll
     for (int i = 0; i < NU; i++) {
       u[i] = ub[k * NU + i];
-      su[i] = (cl == i) ? T(1) : T(0);
+      su[i] = (j == i) ? T(1) : T(0);
     }
+    const int e2 = j + NCOL;                           // second state entry of lanes j = 0, 1 (11, 12)
     if (grads && live) {
-      // LINEAR_LS gradients and the delta-form box of this stage (what gradients() computes), in
+      // LINEAR_LS gradients and the delta-form box of the stage (what gradients() computes), in
       // the same pass: the stage's reference row is read while the integrator runs
-      if (cl < NX) ws[L.q + k * NX + cl] = c.Wq[cl] * (xb[k * NX + cl] - (T)yref[k * NZ + cl]);
-      if (cl < NU) {
-        const T uu = ub[k * NU + cl];
-        ws[L.r + k * NU + cl] = c.Wr[cl] * (uu - (T)yref[k * NZ + NX + cl]);
-        ws[L.lb + k * NU + cl] = c.lbu[cl] - uu;
-        ws[L.ubd + k * NU + cl] = c.ubu[cl] - uu;
-        ws[L.Rt + k * NU + cl] = c.Rd[cl];
+      ws[L.q + k * NX + j] = c.Wq[j] * (xb[k * NX + j] - (T)yref[k * NZ + j]);
+      if (e2 < NX) ws[L.q + k * NX + e2] = c.Wq[e2] * (xb[k * NX + e2] - (T)yref[k * NZ + e2]);
+      if (j < NU) {
+        const T uu = ub[k * NU + j];
+        ws[L.r + k * NU + j] = c.Wr[j] * (uu - (T)yref[k * NZ + NX + j]);
+        ws[L.lb + k * NU + j] = c.lbu[j] - uu;
+        ws[L.ubd + k * NU + j] = c.ubu[j] - uu;
+        ws[L.Rt + k * NU + j] = c.Rd[j];
       }
     }
     erk_column<T, NS>(c, x, u, s, su);
-    if (live && ccol) {
+    if (live) {
 #pragma unroll
-      for (int i = 0; i < NX; i++) M[k * REC + i * M_LD + zc] = s[i];
-    }
-    T xl = x[0];  // every lane of a half holds the same nominal x; lane i writes component i
+      for (int i = 0; i < NX; i++) M[k * REC + i * M_LD + j] = s[i];
+      // defect (every lane of a stage holds the same nominal x): lane j writes component j, lanes
+      // 0 and 1 also 11 and 12; a copy rides in the last column of M_k's rows
+      T xl = x[0];
 #pragma unroll
-    for (int i = 1; i < NX; i++) xl = (cl == i) ? x[i] : xl;
-    if (live && cl < NX) {  // defect; a copy rides in the last column of M_k's rows (staged with the tile)
-      const T bk = xl - xb[(k + 1) * NX + cl];
-      bv[k * NX + cl] = bk;
-      M[k * REC + cl * M_LD + MC_B] = bk;
+      for (int i = 1; i < NCOL; i++) xl = (j == i) ? x[i] : xl;
+      const T b1 = xl - xb[(k + 1) * NX + j];
+      bv[k * NX + j] = b1;
+      M[k * REC + j * M_LD + MC_B] = b1;
+      if (e2 < NX) {
+        const T b2 = ((j == 0) ? x[NCOL] : x[NCOL + 1]) - xb[(k + 1) * NX + e2];
+        bv[k * NX + e2] = b2;
+        M[k * REC + e2 * M_LD + MC_B] = b2;
+      }
     }
   }
   if (grads && lane < NX) ws[L.q + N * NX + lane] = c.We[lane] * (xb[N * NX + lane] - (T)yref_e[lane]);
