@@ -175,6 +175,8 @@ def test_device_mask_invalidate_and_stream_scope(params, O):
     yb, yeb = setpoint_refs(rng, xb, 600, big.hover_thrust)
     xb, yb, yeb = (torch.as_tensor(a, device=dev) for a in (xb, yb, yeb))
     side = torch.cuda.Stream(dev)
+    big.solve(xb, yb, yeb)      # first launch of this instantiation (lazy module load) stays outside
+    big.invalidate()
     torch.cuda.synchronize(dev)
     t0 = time.perf_counter()
     with torch.cuda.stream(side):
