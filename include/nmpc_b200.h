@@ -149,6 +149,37 @@ int nmpc_reset_last_command(nmpc_handle_t *h);
 int nmpc_solve_device(nmpc_handle_t *h, const double *x0, const double *yref, const double *yref_e,
                       double *u0, int32_t *status, double *thrust, double *speed, void *stream);
 
+/* Allocation-free solve.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid allocations).  Same kernel and same results as nmpc_create +
+ * nmpc_solve_device, but there is no handle: the caller owns the warm-start store, and the solver's
+ * scratch memory (per-warp workspaces + the work-queue counter) is a file-scope static __device__
+ * array of NMPC_STATIC_SCRATCH_BYTES that every GPU that loads the library holds until exit.  The
+ * call makes no cudaMalloc / cudaFree / cudaHostAlloc and calls no allocating library routine.
+ *   cfg                       as for nmpc_create (any precision / integrator / horizon within the limit)
+ *   x0, yref, yref_e          inputs, device, as for nmpc_solve_device
+ *   xtraj[batch,N+1,13], utraj[batch,N,4], valid[batch], last_cmd[batch,4]
+ *                             the caller's warm-start store and last valid command, device, IN/OUT,
+ *                             all required (start with valid = 0 and last_cmd = m g / 4)
+ *   u0, status, thrust, speed, qp_iters, sqp_iters   outputs, device, any may be NULL
+ * Limits (NMPC_E_INVALID + nmpc_last_error() beyond them): 1 <= batch <= NMPC_STATIC_MAX_BATCH, and
+ * a horizon whose four per-warp workspaces (one CTA) fit the scratch array (N <= 600 in FP64 does).
+ * The number of problems in flight is what fits the array (N = 20, FP64: 148 CTAs x 4 warps);
+ * problems are handed out in index order.  The per-problem rows are read with plain loads, so the
+ * caller's buffers need no padding and only 8-byte alignment.
+ * ALL calls on one GPU share the array: calls that overlap on the GPU (different streams or
+ * host threads of one process) race -- serialise them on one stream.  The array
+ * keeps the previous call's contents; the only part that must start at zero (the work-queue
+ * counter) is cleared by a memset node on `stream` in front of every launch.  The first call on a
+ * device resolves the array's device address (cudaGetSymbolAddress) and sets the kernel's
+ * shared-memory attribute: make that call outside a stream capture. */
+#define NMPC_STATIC_SCRATCH_BYTES (36u << 20)
+#define NMPC_STATIC_MAX_BATCH 65536
+int nmpc_solve_static(const nmpc_config_t *cfg, int32_t batch, int32_t device, const double *x0,
+                      const double *yref, const double *yref_e, double *xtraj, double *utraj,
+                      uint8_t *valid, double *last_cmd, double *u0, int32_t *status, double *thrust,
+                      double *speed, int32_t *qp_iters, int32_t *sqp_iters, void *stream);
+
 /* Same with HOST buffers (pinned or pageable): H2D copies, solve, D2H copies, stream sync. */
 int nmpc_solve_host(nmpc_handle_t *h, const double *x0, const double *yref, const double *yref_e,
                     double *u0, int32_t *status, double *thrust, double *speed);

@@ -60,6 +60,7 @@ class NmpcRollout(C.Structure):
 
 
 REF_SETPOINT, REF_FIGURE8, NSTATS = 0, 1, 8
+STATIC_SCRATCH_BYTES, STATIC_MAX_BATCH = 36 << 20, 65536   # nmpc_solve_static limits
 
 # every symbol include/nmpc_b200.h declares: (restype, argtypes)
 _vp, _dp, _ip, _bp = C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p
@@ -73,6 +74,10 @@ SYMBOLS = {
     'nmpc_reset_last_command': (C.c_int, [_vp]),
     'nmpc_solve_device': (C.c_int, [_vp, _dp, _dp, _dp, _dp, _ip, _dp, _dp, _vp]),
     'nmpc_solve_host': (C.c_int, [_vp, _dp, _dp, _dp, _dp, _ip, _dp, _dp]),
+    # allocation-free variant (scratch in a static device array): cfg, batch, device, x0, yref, yref_e,
+    # xtraj, utraj, valid, last_cmd, u0, status, thrust, speed, qp_iters, sqp_iters, stream
+    'nmpc_solve_static': (C.c_int, [C.POINTER(NmpcConfig), C.c_int32, C.c_int32, _dp, _dp, _dp, _dp,
+                                    _dp, _bp, _dp, _dp, _ip, _dp, _dp, _ip, _ip, _vp]),
     'nmpc_get_trajectories': (C.c_int, [_vp, _dp, _dp, _bp, C.c_int32]),
     'nmpc_get_stats': (C.c_int, [_vp, _ip, _ip, C.c_int32]),
     'nmpc_set_trajectories': (C.c_int, [_vp, _dp, _dp, _bp]),

@@ -6,6 +6,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
 #include <new>
 
 #include "../../include/nmpc_b200.h"
@@ -655,6 +656,134 @@ int nmpc_solve_device(nmpc_handle_t* h, const double* x0, const double* yref, co
   if (h->cfg.precision == NMPC_PRECISION_F64)
     return launch_solve_T<double>(h, x0, yref, yref_e, u0, status, thrust, speed, st);
   return launch_solve_T<float>(h, x0, yref, yref_e, u0, status, thrust, speed, st);
+}
+
+// ---------------------------------------------------------------- allocation-free solve
+// (no counterpart in the reference, see include/nmpc_b200.h).  g_static_scratch in HOST code is a
+// stand-in symbol, not a device address: the address a kernel may use comes from
+// cudaGetSymbolAddress, once per device with that device current (static_setup).
+extern "C++" {
+constexpr size_t STATIC_HEAD = 256;  // [work-queue counter | pad] in front of the workspaces
+static __device__ __align__(256) unsigned char g_static_scratch[NMPC_STATIC_SCRATCH_BYTES];
+
+constexpr int STATIC_MAX_DEVICES = 64;
+struct StaticDevice {
+  unsigned char* scratch;  // device address of g_static_scratch on this device
+  int sm_count;
+  int occ[8];              // resident CTAs per SM of the instantiation [precision * 4 + variant], 0 = not set up
+};
+static StaticDevice g_static_dev[STATIC_MAX_DEVICES];
+static std::mutex g_static_mutex;
+
+template <typename T, int NS, int NF>
+static int launch_static(const nmpc_config_t* cfg, int batch, int device, int key, SolveArgs<T>& A,
+                         cudaStream_t st) {
+  StaticDevice& D = g_static_dev[device];
+  const size_t smem = ((size_t)WARPS * smem_elems_per_warp() + VBLOCK_ELEMS) * sizeof(T);
+  auto kern = nmpc_solve_kernel<T, NS, NF>;
+  {
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (!D.scratch) {
+      void* p = nullptr;
+      CK(cudaGetSymbolAddress(&p, g_static_scratch));
+      CK(cudaDeviceGetAttribute(&D.sm_count, cudaDevAttrMultiProcessorCount, device));
+      D.scratch = static_cast<unsigned char*>(p);
+    }
+    if (!D.occ[key]) {
+      CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      int occ = 0;
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, WARPS * 32, smem));
+      D.occ[key] = occ < 1 ? 1 : occ;
+    }
+  }
+  const WsLayout L = make_layout(cfg->N);
+  const size_t slot_bytes = (size_t)L.total * sizeof(T);
+  const size_t fit = (NMPC_STATIC_SCRATCH_BYTES - STATIC_HEAD) / (slot_bytes * WARPS);  // CTAs
+  if (fit < 1) {
+    snprintf(g_err, sizeof(g_err),
+             "nmpc_solve_static: horizon N = %d needs %zu bytes of workspace per CTA, the static "
+             "scratch array holds %zu (NMPC_STATIC_SCRATCH_BYTES)",
+             cfg->N, slot_bytes * WARPS, (size_t)NMPC_STATIC_SCRATCH_BYTES - STATIC_HEAD);
+    return NMPC_E_INVALID;
+  }
+  int grid = D.sm_count * D.occ[key];
+  if ((size_t)grid > fit) grid = (int)fit;
+  if (grid > batch) grid = batch;
+  int* counter = reinterpret_cast<int*>(D.scratch);
+  A.ws = reinterpret_cast<T*>(D.scratch + STATIC_HEAD);
+  CK(cudaMemsetAsync(counter, 0, sizeof(int), st));  // the one part of the array that must start at 0
+  kern<<<grid, WARPS * 32, smem, st>>>(A, L, counter);
+  CK(cudaGetLastError());
+  return NMPC_OK;
+}
+
+template <typename T>
+static int solve_static_T(const nmpc_config_t* cfg, int batch, int device, const double* x0,
+                          const double* yref, const double* yref_e, double* xtraj, double* utraj,
+                          uint8_t* valid, double* last_cmd, double* u0, int32_t* status,
+                          double* thrust, double* speed, int32_t* qp_iters, int32_t* sqp_iters,
+                          cudaStream_t st) {
+  SolveArgs<T> A;
+  A.cfg = make_devcfg<T>(*cfg);
+  A.batch = batch;
+  A.x0 = x0;
+  A.yref = yref;
+  A.yref_e = yref_e;
+  A.xtraj = xtraj;
+  A.utraj = utraj;
+  A.valid = valid;
+  A.last_cmd = last_cmd;
+  A.u0 = u0;
+  A.status = status;
+  A.thrust = thrust;
+  A.speed = speed;
+  A.qp_iters = qp_iters;
+  A.sqp_iters = sqp_iters;
+  A.ws = nullptr;
+  A.order = nullptr;  // index order: the longest-expected-first order would need per-batch scratch
+  A.stage = 0;        // plain loads: no alignment or padding demands on the caller's buffers
+  A.poison = 0;
+  const int p4 = (sizeof(T) == 4 ? 4 : 0);
+  const bool fixed = cfg->N == N_FIXED && cfg->integ_ns == 2 && !getenv("NMPC_B200_GENERIC_N");
+  switch (cfg->integ_ns) {
+    case 1: return launch_static<T, 1, 0>(cfg, batch, device, p4 + 0, A, st);
+    case 2:
+      return fixed ? launch_static<T, 2, N_FIXED>(cfg, batch, device, p4 + 1, A, st)
+                   : launch_static<T, 2, 0>(cfg, batch, device, p4 + 2, A, st);
+    default: return launch_static<T, 4, 0>(cfg, batch, device, p4 + 3, A, st);
+  }
+}
+}  // extern "C++"
+
+int nmpc_solve_static(const nmpc_config_t* cfg, int32_t batch, int32_t device, const double* x0,
+                      const double* yref, const double* yref_e, double* xtraj, double* utraj,
+                      uint8_t* valid, double* last_cmd, double* u0, int32_t* status, double* thrust,
+                      double* speed, int32_t* qp_iters, int32_t* sqp_iters, void* stream) {
+  if (validate(cfg) != NMPC_OK) {
+    snprintf(g_err, sizeof(g_err), "nmpc_solve_static: invalid configuration");
+    return NMPC_E_INVALID;
+  }
+  if (batch < 1 || batch > NMPC_STATIC_MAX_BATCH) {
+    snprintf(g_err, sizeof(g_err), "nmpc_solve_static: batch %d outside 1..%d (NMPC_STATIC_MAX_BATCH)",
+             (int)batch, NMPC_STATIC_MAX_BATCH);
+    return NMPC_E_INVALID;
+  }
+  if (!x0 || !yref || !yref_e || !xtraj || !utraj || !valid || !last_cmd) {
+    snprintf(g_err, sizeof(g_err), "nmpc_solve_static: null input or warm-start store pointer");
+    return NMPC_E_INVALID;
+  }
+  if (device < 0 || device >= STATIC_MAX_DEVICES) {
+    snprintf(g_err, sizeof(g_err), "nmpc_solve_static: device %d outside 0..%d", (int)device,
+             STATIC_MAX_DEVICES - 1);
+    return NMPC_E_INVALID;
+  }
+  CK(cudaSetDevice(device));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (cfg->precision == NMPC_PRECISION_F64)
+    return solve_static_T<double>(cfg, batch, device, x0, yref, yref_e, xtraj, utraj, valid,
+                                  last_cmd, u0, status, thrust, speed, qp_iters, sqp_iters, st);
+  return solve_static_T<float>(cfg, batch, device, x0, yref, yref_e, xtraj, utraj, valid, last_cmd,
+                               u0, status, thrust, speed, qp_iters, sqp_iters, st);
 }
 
 int nmpc_solve_host(nmpc_handle_t* h, const double* x0, const double* yref, const double* yref_e,
