@@ -173,7 +173,7 @@ int nmpc_solve_device(nmpc_handle_t *h, const double *x0, const double *yref, co
  * counter) is cleared by a memset node on `stream` in front of every launch.  The first call on a
  * device resolves the array's device address (cudaGetSymbolAddress) and sets the kernel's
  * shared-memory attribute: make that call outside a stream capture. */
-#define NMPC_STATIC_SCRATCH_BYTES (36u << 20)
+#define NMPC_STATIC_SCRATCH_BYTES (40u << 20)
 #define NMPC_STATIC_MAX_BATCH 65536
 int nmpc_solve_static(const nmpc_config_t *cfg, int32_t batch, int32_t device, const double *x0,
                       const double *yref, const double *yref_e, double *xtraj, double *utraj,

@@ -60,7 +60,7 @@ class NmpcRollout(C.Structure):
 
 
 REF_SETPOINT, REF_FIGURE8, NSTATS = 0, 1, 8
-STATIC_SCRATCH_BYTES, STATIC_MAX_BATCH = 36 << 20, 65536   # nmpc_solve_static limits
+STATIC_SCRATCH_BYTES, STATIC_MAX_BATCH = 40 << 20, 65536   # nmpc_solve_static limits
 
 # every symbol include/nmpc_b200.h declares: (restype, argtypes)
 _vp, _dp, _ip, _bp = C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p

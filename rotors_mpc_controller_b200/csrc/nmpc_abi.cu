@@ -31,6 +31,8 @@ namespace {
 #endif
 constexpr int WARPS = CTA_WARPS;  // warps (= problems in flight) per CTA
 constexpr size_t SMALL_HOST_BYTES = 256 * 1024;  // nmpc_solve_host packs batches up to this input size
+constexpr size_t ZERO_COPY_BYTES = 16 * 1024;    // ... and up to this size the kernel reads / writes the
+                                                 // pinned mirrors directly (no copy nodes on the stream)
 
 constexpr int smem_elems_per_warp() { return smem_tile_elems(); }
 
@@ -63,6 +65,10 @@ __global__ void __maxnreg__(sizeof(T) == 4 ? NMPC_MAXNREG_F32 : NMPC_MAXNREG)
   // batch smaller than the number of resident warps spreads evenly over the SMs (and schedulers)
   // instead of filling the first CTAs.  Afterwards a dynamic queue: iteration counts differ per
   // problem, so problems are handed out one at a time instead of in a fixed stride.
+  // (Measured and dropped: positions dealt out so that every scheduler gets one problem of the
+  // longest, the middle and the shortest third of the first round -- no change, the queue keeps
+  // every scheduler full until it is empty either way; and the block scheduler does not place CTA b
+  // on SM b mod 148, see scripts/micro/cta_placement.cu.)
   int pos = warp * gridDim.x + blockIdx.x;
   while (pos < A.batch) {
     int prob = pos;
@@ -71,6 +77,7 @@ __global__ void __maxnreg__(sizeof(T) == 4 ? NMPC_MAXNREG_F32 : NMPC_MAXNREG)
       prob = __shfl_sync(FULL, prob, 0);
     }
     solve_one<T, NS, NF>(A, L, ws, sm, prob, lane);
+    if (A.batch <= (int)gridDim.x * WARPS) break;  // one round: the queue is not used (nor reset by the host)
     if (lane == 0) pos = atomicAdd(work_counter, 1) + gridDim.x * WARPS;
     pos = __shfl_sync(FULL, pos, 0);
   }
@@ -287,6 +294,8 @@ struct nmpc_handle {
   // outputs [u0 | thrust | speed | status] (sections padded to 16 bytes), so that a small batch moves
   // with one H2D and one D2H copy through the pinned host mirrors pin_in / pin_out
   unsigned char *s_in, *s_out, *pin_in, *pin_out;
+  unsigned char *zc_in, *zc_out;  // device aliases of the pinned mirrors (tiny batches: zero-copy), else null
+  unsigned char* last_out;        // where the last handle-owned outputs were written (s_out or zc_out)
   size_t in_bytes, out_bytes, off_yref, off_yref_e, off_thrust, off_speed, off_status;
   double *s_x0, *s_yref, *s_yref_e, *s_u0, *s_thrust, *s_speed;
   int* s_status;
@@ -439,8 +448,12 @@ static int create_impl(nmpc_handle* h, const nmpc_config_t* cfg, int batch, int 
   h->s_speed = reinterpret_cast<double*>(h->s_out + h->off_speed);
   h->s_status = reinterpret_cast<int*>(h->s_out + h->off_status);
   if (h->in_bytes <= SMALL_HOST_BYTES) {  // latency path of nmpc_solve_host (e.g. the single vehicle)
-    CK(cudaHostAlloc(&h->pin_in, h->in_bytes, cudaHostAllocDefault));
-    CK(cudaHostAlloc(&h->pin_out, h->out_bytes, cudaHostAllocDefault));
+    CK(cudaHostAlloc(&h->pin_in, h->in_bytes, cudaHostAllocMapped));
+    CK(cudaHostAlloc(&h->pin_out, h->out_bytes, cudaHostAllocMapped));
+    if (h->in_bytes <= ZERO_COPY_BYTES && !getenv("NMPC_B200_NO_ZERO_COPY")) {
+      CK(cudaHostGetDevicePointer(reinterpret_cast<void**>(&h->zc_in), h->pin_in, 0));
+      CK(cudaHostGetDevicePointer(reinterpret_cast<void**>(&h->zc_out), h->pin_out, 0));
+    }
   }
   CK(cudaMalloc(&h->s_mask, B));
   cudaStream_t st = h->stream;
@@ -610,7 +623,7 @@ static int launch_solve(nmpc_handle* h, const double* x0, const double* yref, co
   const size_t smem = solve_smem_bytes<T>(h);
   // one workspace per handle: a solve on another stream than the previous one queues behind it
   CK(cudaStreamWaitEvent(st, h->ev_last, 0));
-  CK(cudaMemsetAsync(h->counter, 0, sizeof(int), st));
+  if (h->batch > h->nslots) CK(cudaMemsetAsync(h->counter, 0, sizeof(int), st));  // else: one round, no queue
   // longest-expected-first dispatch when the launch is a few waves of very unequal problems
   const int disp = h->cfg.dispatch;
   const bool lpt = disp == NMPC_DISPATCH_LPT ||
@@ -798,11 +811,23 @@ int nmpc_solve_host(nmpc_handle_t* h, const double* x0, const double* yref, cons
     memcpy(h->pin_in, x0, B * NX * sizeof(double));
     memcpy(h->pin_in + h->off_yref, yref, B * N * NZ * sizeof(double));
     memcpy(h->pin_in + h->off_yref_e, yref_e, B * NX * sizeof(double));
-    CK(cudaMemcpyAsync(h->s_in, h->pin_in, h->in_bytes, cudaMemcpyHostToDevice, st));
-    int rc = nmpc_solve_device(h, h->s_x0, h->s_yref, h->s_yref_e, h->s_u0, h->s_status, h->s_thrust,
-                               h->s_speed, st);
+    // a tiny batch (the single vehicle): the kernel reads the inputs from the pinned mirror and
+    // writes its outputs there (one PCIe round trip for the staged rows, posted writes) -- no copy
+    // nodes in front of and behind the kernel
+    const bool zc = h->zc_in != nullptr;
+    unsigned char* in = zc ? h->zc_in : h->s_in;
+    unsigned char* out = zc ? h->zc_out : h->s_out;
+    h->last_out = out;
+    if (!zc) CK(cudaMemcpyAsync(h->s_in, h->pin_in, h->in_bytes, cudaMemcpyHostToDevice, st));
+    int rc = nmpc_solve_device(h, reinterpret_cast<double*>(in),
+                               reinterpret_cast<double*>(in + h->off_yref),
+                               reinterpret_cast<double*>(in + h->off_yref_e),
+                               reinterpret_cast<double*>(out),
+                               reinterpret_cast<int32_t*>(out + h->off_status),
+                               reinterpret_cast<double*>(out + h->off_thrust),
+                               reinterpret_cast<double*>(out + h->off_speed), st);
     if (rc != NMPC_OK) return rc;
-    CK(cudaMemcpyAsync(h->pin_out, h->s_out, h->out_bytes, cudaMemcpyDeviceToHost, st));
+    if (!zc) CK(cudaMemcpyAsync(h->pin_out, h->s_out, h->out_bytes, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     if (u0) memcpy(u0, h->pin_out, B * NU * sizeof(double));
     if (thrust) memcpy(thrust, h->pin_out + h->off_thrust, B * NU * sizeof(double));
@@ -810,6 +835,7 @@ int nmpc_solve_host(nmpc_handle_t* h, const double* x0, const double* yref, cons
     if (status) memcpy(status, h->pin_out + h->off_status, B * sizeof(int));
     return NMPC_OK;
   }
+  h->last_out = h->s_out;
   CK(cudaMemcpyAsync(h->s_x0, x0, B * NX * sizeof(double), cudaMemcpyHostToDevice, st));
   CK(cudaMemcpyAsync(h->s_yref, yref, B * N * NZ * sizeof(double), cudaMemcpyHostToDevice, st));
   CK(cudaMemcpyAsync(h->s_yref_e, yref_e, B * NX * sizeof(double), cudaMemcpyHostToDevice, st));
@@ -1008,6 +1034,7 @@ int nmpc_rollout_device(nmpc_handle_t* h, const nmpc_rollout_t* run, void* strea
   }
   CK(cudaSetDevice(h->device));
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  h->last_out = h->s_out;
   const int N = h->cfg.N;
   // state handed to the first solve: normalised copy of the plant state (substeps = 0)
   nmpc_plant_t norm_only = run->plant;
@@ -1043,10 +1070,11 @@ int nmpc_rollout_device(nmpc_handle_t* h, const nmpc_rollout_t* run, void* strea
 int nmpc_last_outputs(nmpc_handle_t* h, const double** u0, const int32_t** status,
                       const double** thrust, const double** speed) {
   if (!h) return NMPC_E_INVALID;
-  if (u0) *u0 = h->s_u0;
-  if (status) *status = h->s_status;
-  if (thrust) *thrust = h->s_thrust;
-  if (speed) *speed = h->s_speed;
+  const unsigned char* o = h->last_out ? h->last_out : h->s_out;
+  if (u0) *u0 = reinterpret_cast<const double*>(o);
+  if (status) *status = reinterpret_cast<const int32_t*>(o + h->off_status);
+  if (thrust) *thrust = reinterpret_cast<const double*>(o + h->off_thrust);
+  if (speed) *speed = reinterpret_cast<const double*>(o + h->off_speed);
   return NMPC_OK;
 }
 

@@ -53,6 +53,7 @@ struct WsLayout {
   int xb, q, b, dx;                                                // x-type vectors
   int ub, r, lb, ubd, du, ua, tl, tu, ll, lu, rbl0, rbu0, ru0;    // u-type vectors
   int dtl, dtu, dll, dlu, Rt, rt, dr, itl, itu;
+  int ck;  // NCK cost-to-go checkpoints (P, p) of the factor sweep, CK_ELEMS each
   int total;
 };
 
@@ -71,6 +72,14 @@ constexpr int REC_F = REC_K + NU * K_LD;      // 212: offset of the factors (10 
 constexpr int REC = REC_F + 16;               // 228 elements per stage
 // column of a row of M_k that holds dx+/d(state j), j = 6..12 (q, w)
 __host__ __device__ constexpr int mcol_of_state(int j) { return j - 6 + MC_Q; }
+
+// Checkpoints of the backward recursion: the cost-to-go (P_c, p_c) at NCK stages c = ck_stage(N, j).
+// P_c depends on the stages >= c only, so when the active set of a QP changes at stages <= kmax the
+// next factorisation restarts from the lowest checkpoint above kmax instead of the terminal stage
+// (as_solve): the stages above it would be recomputed to the same bits.
+constexpr int NCK = 4;
+constexpr int CK_ELEMS = (NX + 1) * 14;  // 13 rows of P (14 wide) + p (14)
+__host__ __device__ constexpr int ck_stage(int N, int j) { return ((j + 1) * N) / (NCK + 1); }
 
 __host__ __device__ inline WsLayout make_layout(int N) {
   WsLayout L;
@@ -113,6 +122,7 @@ __host__ __device__ inline WsLayout make_layout(int N) {
   L.dr = take(nu);
   L.itl = take(nu);
   L.itu = take(nu);
+  L.ck = take(NCK * CK_ELEMS);
   L.total = o;
   return L;
 }
@@ -425,7 +435,7 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
   if (!skip0) {
     res0 = T(0);  // b and q are met exactly by the phase-0 point
     PROF_ADD(PH_ELEM);
-    const bool ok0 = factor_sweep<T, NF>(c, ws, L, sm, lane, T(1), false);
+    const bool ok0 = factor_sweep<T, NF, false>(c, ws, L, sm, lane, T(1), false, -1);
     PROF_ADD(PH_FACTOR);
     it = 1;
     if (!ok0) {
@@ -527,7 +537,7 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
     __syncwarp();
     const T rq = skip0 ? rho : T(0);
     PROF_ADD(PH_ELEM);
-    const bool ok = factor_sweep<T, NF>(c, ws, L, sm, lane, rq, false);
+    const bool ok = factor_sweep<T, NF, false>(c, ws, L, sm, lane, rq, false, -1);
     PROF_ADD(PH_FACTOR);
     if (!ok) {
       // FP32 precision floor: once the complementarity is below 1e-6 a lost pivot means the
@@ -711,11 +721,16 @@ __device__ __forceinline__ bool as_solve(const DevCfg<T>& c, T* __restrict__ ws,
     any = any || lo || up;
   }
   any = __any_sync(FULL, any);
+  int cj = -1;  // checkpoint the next factorisation restarts from (-1: terminal stage, full sweep)
   for (int rep = 0; rep < NMPC_AS_MAXIT && rep < c.qp_iter_max; rep++) {  // iter_max caps every QP method
     __syncwarp();
     *tried += 1;
     PROF_ADD(PH_ELEM);
-    bool ok = factor_sweep<T, NF>(c, ws, L, sm, lane, T(1), any);
+    // checkpointed sweep: restarts below the last change of the set (cj), stores the checkpoints it passes.
+    // (Measured: choosing the plain instantiation for first factorisations that are likely to be
+    // accepted -- warm-started RTI -- saves the stores, 0.5 %, but two copies of the sweep in one
+    // solve cost more in the instruction cache.)
+    bool ok = factor_sweep<T, NF, true>(c, ws, L, sm, lane, T(1), any, cj);
     PROF_ADD(PH_FACTOR);
     if (!ok) return false;
     forward_sweep<T, NF>(c, ws, L, sm, lane, T(1), false, true, false, L.kff, L.dx, L.du);
@@ -745,6 +760,7 @@ __device__ __forceinline__ bool as_solve(const DevCfg<T>& c, T* __restrict__ ws,
     }
     // primal-dual update of the set
     bool changed = false, any_new = false;
+    int kmax = -1;  // last stage whose rows change
     _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
       const T code = ws[L.dtl + i], du = ws[L.du + i], lb = ws[L.lb + i], ub = ws[L.ubd + i];
       T ncode = code;
@@ -752,12 +768,20 @@ __device__ __forceinline__ bool as_solve(const DevCfg<T>& c, T* __restrict__ ws,
       else if (any && code == T(1) && !(ws[L.dll + i] >= T(0))) ncode = T(0);
       else if (any && code == T(2) && !(ws[L.dlu + i] >= T(0))) ncode = T(0);
       changed = changed || (ncode != code);
+      if (ncode != code) kmax = i >> 2;  // i ascends
       any_new = any_new || (ncode != T(0));
       ws[L.dtl + i] = ncode;
       ws[L.dr + i] = ncode == T(1) ? lb : (ncode == T(2) ? ub : nan);
     }
     if (!__any_sync(FULL, changed)) return false;  // NaN data / no progress: the interior point reports it
     any = __any_sync(FULL, any_new);
+    // stages above the last changed one keep their factorisation: restart from the lowest
+    // checkpoint above it
+    kmax = __reduce_max_sync(FULL, kmax);
+    cj = -1;
+#pragma unroll
+    for (int j = NCK - 1; j >= 0; j--)
+      if (ck_stage(N, j) > kmax && ck_stage(N, j) < N) cj = j;
   }
   return false;
 }
