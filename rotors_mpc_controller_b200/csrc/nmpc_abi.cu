@@ -358,7 +358,8 @@ const DevCfg<float>& devcfg_of<float>(const nmpc_handle* h) { return h->dc32; }
 // integrator runs the fixed-horizon instantiation.
 constexpr int N_FIXED = 20;
 static bool use_fixed_horizon(const nmpc_handle* h) {
-  return h->cfg.N == N_FIXED && h->cfg.integ_ns == 2 && !getenv("NMPC_B200_GENERIC_N");
+  return h->cfg.N == N_FIXED && h->cfg.integ_ns == 2 && h->cfg.integ_steps == 2 &&
+         !getenv("NMPC_B200_GENERIC_N");
 }
 
 template <typename T, int NS, int NF>
@@ -757,7 +758,8 @@ static int solve_static_T(const nmpc_config_t* cfg, int batch, int device, const
   A.stage = 0;        // plain loads: no alignment or padding demands on the caller's buffers
   A.poison = 0;
   const int p4 = (sizeof(T) == 4 ? 4 : 0);
-  const bool fixed = cfg->N == N_FIXED && cfg->integ_ns == 2 && !getenv("NMPC_B200_GENERIC_N");
+  const bool fixed = cfg->N == N_FIXED && cfg->integ_ns == 2 && cfg->integ_steps == 2 &&
+                     !getenv("NMPC_B200_GENERIC_N");
   switch (cfg->integ_ns) {
     case 1: return launch_static<T, 1, 0>(cfg, batch, device, p4 + 0, A, st);
     case 2:

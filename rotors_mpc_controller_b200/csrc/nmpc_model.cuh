@@ -31,6 +31,16 @@ struct DevCfg {
   T sqp_tol, ipm_tol;
 };
 
+// Two consecutive elements moved by one 16-byte (FP64) / 8-byte (FP32) access.
+template <typename T>
+struct alignas(2 * sizeof(T)) Pair {
+  T a, b;
+};
+template <typename T>
+__device__ __forceinline__ Pair<T> ld2(const T* p) {
+  return *reinterpret_cast<const Pair<T>*>(p);
+}
+
 // f(x,u) and its directional derivative df = F_x sx + F_u su   (controller.py:286-346).
 template <typename T>
 __device__ __forceinline__ void model_jvp(const DevCfg<T>& c, const T (&x)[NX], const T (&u)[NU],

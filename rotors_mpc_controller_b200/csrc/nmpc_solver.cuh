@@ -269,12 +269,157 @@ __device__ __forceinline__ bool finite_(T v) {
 // nothing in the model depends on the position or the velocity, so the p and v columns of A_k are
 // constants that are never formed: 11 columns (u, q, w) per stage are integrated, one per lane,
 // as directional derivatives of the ERK map (no Jacobian matrix is built).
+// Linearisation with the nominal trajectory integrated ONCE per stage (explicit midpoint, the
+// reference's integrator).  The column-per-lane mapping of linearize() below integrates the nominal
+// state redundantly in every one of the 11 lanes of a stage -- 43 % of the model arithmetic.  Here
+//   phase A: lane k integrates the nominal state of stage k and leaves the points at which the
+//            model is evaluated (start and midpoint of every sub-step) in the warp's idle sweep tile,
+//            together with the defect b_k;
+//   phase B: the 11 N (stage, column) items, dealt out flat over the lanes as before, integrate
+//            their sensitivity column only: the directional derivative of the model at the stored points
+//            (model_jvp with its nominal outputs unused: the compiler drops them).
+// Same expressions in the same order as erk_column, so M_k and b_k are the same to the bit.
+// Tile: [x iterate (N+1) x 13 | u iterate N x 4 | points N x (2 steps - 1) x 14 (padded rows)].
+constexpr int PT_LD = 14;
+template <typename T, int NF>
+__device__ __forceinline__ bool linearize_fits_points(const DevCfg<T>& c, int N) {
+  const int steps = NF > 0 ? 2 : c.integ_steps;
+  const int base = ((N + 1) * NX + N * NU + 1) & ~1;
+  return N <= 32 && base + (2 * steps - 1) * N * PT_LD <= SmemLayout::bar;
+}
+template <typename T, int NF>
+__device__ __forceinline__ void linearize_points(const DevCfg<T>& c, T* __restrict__ ws,
+                                                 const WsLayout& Lr, T* __restrict__ sm, int lane,
+                                                 const double* __restrict__ yref,
+                                                 const double* __restrict__ yref_e, bool grads) {
+  NMPC_FIXED(c)
+  const int steps = NF > 0 ? 2 : c.integ_steps;
+  const int npts = 2 * steps - 1;
+  const int nxv = (N + 1) * NX, nuv = N * NU;
+  T* sx = sm;
+  T* su_ = sm + nxv;
+  T* pts = sm + ((nxv + nuv + 1) & ~1);
+  {
+    const T* gx = ws + L.xb;
+    const T* gu = ws + L.ub;
+    _Pragma("unroll 9") for (int i = lane; i < nxv; i += 32) sx[i] = gx[i];
+    _Pragma("unroll 3") for (int i = lane; i < nuv; i += 32) su_[i] = gu[i];
+  }
+  __syncwarp();
+  T* M = ws + L.M;
+  T* bv = ws + L.b;
+  const T h = c.h;
+  // phase A: nominal trajectory of stage `lane`
+  if (lane < N) {
+    const int k = lane;
+    T x[NX], u[NU], f[NX];
+#pragma unroll
+    for (int i = 0; i < NX; i++) x[i] = sx[k * NX + i];
+#pragma unroll
+    for (int i = 0; i < NU; i++) u[i] = su_[k * NU + i];
+    T* pk = pts + k * npts * PT_LD;
+    for (int step = 0; step < steps; step++) {
+      T xs[NX];
+      model_f(c, x, u, f);
+#pragma unroll
+      for (int i = 0; i < NX; i++) {
+        xs[i] = x[i] + (T(0.5) * h) * f[i];
+        pk[(2 * step) * PT_LD + i] = xs[i];
+      }
+      model_f(c, xs, u, f);
+#pragma unroll
+      for (int i = 0; i < NX; i++) x[i] += h * f[i];
+      if (step + 1 < steps) {
+#pragma unroll
+        for (int i = 0; i < NX; i++) pk[(2 * step + 1) * PT_LD + i] = x[i];
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < NX; i++) {  // defect; a copy rides in the last column of M_k's rows
+      const T b = x[i] - sx[(k + 1) * NX + i];
+      bv[k * NX + i] = b;
+      M[k * REC + i * M_LD + MC_B] = b;
+    }
+  }
+  __syncwarp();
+  // phase B: sensitivity columns
+  constexpr int NCOL = NZ - 6;
+  const int total = N * NCOL;
+  for (int base = 0; base < total; base += 32) {
+    const bool live = base + lane < total;
+    const int item = live ? base + lane : total - 1;
+    const int k = item / NCOL, j = item - NCOL * k;
+    T x[NX], u[NU], s[NX], su[NU], f[NX], dk[NX];
+#pragma unroll
+    for (int i = 0; i < NX; i++) {
+      x[i] = sx[k * NX + i];
+      s[i] = (j >= NU && i == j + 2) ? T(1) : T(0);   // column j >= 4 is state j + 2 (q, w = 6..12)
+    }
+#pragma unroll
+    for (int i = 0; i < NU; i++) {
+      u[i] = su_[k * NU + i];
+      su[i] = (j == i) ? T(1) : T(0);
+    }
+    const int e2 = j + NCOL;                           // second state entry of lanes j = 0, 1 (11, 12)
+    if (grads && live) {  // LS gradients and the delta-form box of the stage, see linearize()
+      ws[L.q + k * NX + j] = c.Wq[j] * (sx[k * NX + j] - (T)yref[k * NZ + j]);
+      if (e2 < NX) ws[L.q + k * NX + e2] = c.Wq[e2] * (sx[k * NX + e2] - (T)yref[k * NZ + e2]);
+      if (j < NU) {
+        const T uu = su_[k * NU + j];
+        ws[L.r + k * NU + j] = c.Wr[j] * (uu - (T)yref[k * NZ + NX + j]);
+        ws[L.lb + k * NU + j] = c.lbu[j] - uu;
+        ws[L.ubd + k * NU + j] = c.ubu[j] - uu;
+        ws[L.Rt + k * NU + j] = c.Rd[j];
+      }
+    }
+    const T* pk = pts + k * npts * PT_LD;
+    for (int step = 0; step < steps; step++) {
+      T ss[NX];
+      model_jvp(c, x, u, s, su, f, dk);               // at the start of the sub-step
+#pragma unroll
+      for (int i = 0; i < NX; i++) ss[i] = s[i] + (T(0.5) * h) * dk[i];
+      {
+        const T* pm = pk + (2 * step) * PT_LD;        // midpoint
+#pragma unroll
+        for (int cc = 0; cc < 6; cc++) {
+          const Pair<T> v = ld2(pm + 2 * cc);
+          x[2 * cc] = v.a;
+          x[2 * cc + 1] = v.b;
+        }
+        x[12] = pm[12];
+      }
+      model_jvp(c, x, u, ss, su, f, dk);
+#pragma unroll
+      for (int i = 0; i < NX; i++) s[i] += h * dk[i];
+      if (step + 1 < steps) {
+        const T* pn = pk + (2 * step + 1) * PT_LD;    // start of the next sub-step
+#pragma unroll
+        for (int cc = 0; cc < 6; cc++) {
+          const Pair<T> v = ld2(pn + 2 * cc);
+          x[2 * cc] = v.a;
+          x[2 * cc + 1] = v.b;
+        }
+        x[12] = pn[12];
+      }
+    }
+    if (live) {
+#pragma unroll
+      for (int i = 0; i < NX; i++) M[k * REC + i * M_LD + j] = s[i];
+    }
+  }
+  if (grads && lane < NX) ws[L.q + N * NX + lane] = c.We[lane] * (sx[N * NX + lane] - (T)yref_e[lane]);
+}
+
 template <typename T, int NS, int NF>
 __device__ __forceinline__ void linearize(const DevCfg<T>& c, T* __restrict__ ws,
                                           const WsLayout& Lr, T* __restrict__ sm, int lane,
                                           const double* __restrict__ yref,
                                           const double* __restrict__ yref_e, bool grads) {
   NMPC_FIXED(c)
+  if (NS == 2 && linearize_fits_points<T, NF>(c, N)) {  // nominal trajectory once per stage
+    linearize_points<T, NF>(c, ws, Lr, sm, lane, yref, yref_e, grads);
+    return;
+  }
   // The iterate is read stage by stage below (17 broadcast loads per pass, each pass would wait
   // for L2): when it fits the (idle) stage buffers it is copied to shared memory once, with all
   // loads in flight together.
