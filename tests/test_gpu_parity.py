@@ -120,6 +120,31 @@ def test_active_bounds_batch(params, O):
         assert np.max(np.abs(ut - ob.utraj)) < TOL_U
 
 
+@pytest.mark.parametrize('N,steps', [(1, 2), (2, 2), (3, 2), (4, 2), (5, 2), (7, 2), (19, 2), (21, 2),
+                                     (12, 3), (20, 1), (32, 1), (33, 1)])
+def test_horizons_and_substeps_with_active_bounds(params, O, N, steps):
+    """Round-2 code paths that depend on the horizon and on the integrator sub-steps:
+    the checkpoints of the factor sweep sit at stages j N / 5 (several coincide for N < 5, the
+    restart logic must skip them), and the linearisation keeps the nominal points of a stage in
+    the sweep tile when they fit (N <= 20 at 2 sub-steps, N <= 32 at one; above: column-per-lane
+    integration).  Aggressive problems, so the active-set iterations do re-solve."""
+    B = 96
+    ctl, p = _mk(params, B, horizon_steps=N, integrator_steps=steps)
+    rng = np.random.default_rng(100 * N + steps)
+    x0, yref, yref_e = aggressive(rng, B, N, ctl.hover_thrust)
+    ob = O.OracleBatch(O.config_from_params(p, integ_steps=steps), B)
+    for step in range(2):   # cold, then warm from the stored trajectories
+        u0, st = ctl.solve(x0, yref, yref_e)
+        ur, sr, _, _ = ob.solve(x0, yref, yref_e)
+        assert np.array_equal(st, sr)
+        assert np.max(np.abs(u0 - ur)) < TOL_U
+        assert np.array_equal(ctl.stats()['qp_iters'], ob.qp_iters)
+        xt, ut, _ = ctl.trajectories()
+        assert np.max(np.abs(xt - ob.xtraj)) < TOL_U and np.max(np.abs(ut - ob.utraj)) < TOL_U
+    assert ob.qp_iters.max() >= 2   # some problem needed more than one factorisation
+    ctl.close()
+
+
 def test_explicit_thrust_limits_override(params, O):
     """the YAML's [4,20] N box (dead config in the reference) as an opt-in."""
     B, N = 64, 20
