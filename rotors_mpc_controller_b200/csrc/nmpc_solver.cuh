@@ -274,7 +274,7 @@ __device__ __forceinline__ bool finite_(T v) {
 // state redundantly in every one of the 11 lanes of a stage -- 43 % of the model arithmetic.  Here
 //   phase A: lane k integrates the nominal state of stage k and leaves the points at which the
 //            model is evaluated (start and midpoint of every sub-step) in the warp's idle sweep tile,
-//            together with the defect b_k;
+//            together with the defect b_k; it also writes the LS gradients and the box of its stage;
 //   phase B: the 11 N (stage, column) items, dealt out flat over the lanes as before, integrate
 //            their sensitivity column only: the directional derivative of the model at the stored points
 //            (model_jvp with its nominal outputs unused: the compiler drops them).
@@ -317,6 +317,18 @@ __device__ __forceinline__ void linearize_points(const DevCfg<T>& c, T* __restri
     for (int i = 0; i < NX; i++) x[i] = sx[k * NX + i];
 #pragma unroll
     for (int i = 0; i < NU; i++) u[i] = su_[k * NU + i];
+    if (grads) {  // LS gradients and the delta-form box of the stage (what gradients() computes)
+      const double* yk = yref + k * NZ;
+#pragma unroll
+      for (int i = 0; i < NX; i++) ws[L.q + k * NX + i] = c.Wq[i] * (x[i] - (T)yk[i]);
+#pragma unroll
+      for (int i = 0; i < NU; i++) {
+        ws[L.r + k * NU + i] = c.Wr[i] * (u[i] - (T)yk[NX + i]);
+        ws[L.lb + k * NU + i] = c.lbu[i] - u[i];
+        ws[L.ubd + k * NU + i] = c.ubu[i] - u[i];
+        ws[L.Rt + k * NU + i] = c.Rd[i];
+      }
+    }
     T* pk = pts + k * npts * PT_LD;
     for (int step = 0; step < steps; step++) {
       T xs[NX];
@@ -359,18 +371,6 @@ __device__ __forceinline__ void linearize_points(const DevCfg<T>& c, T* __restri
     for (int i = 0; i < NU; i++) {
       u[i] = su_[k * NU + i];
       su[i] = (j == i) ? T(1) : T(0);
-    }
-    const int e2 = j + NCOL;                           // second state entry of lanes j = 0, 1 (11, 12)
-    if (grads && live) {  // LS gradients and the delta-form box of the stage, see linearize()
-      ws[L.q + k * NX + j] = c.Wq[j] * (sx[k * NX + j] - (T)yref[k * NZ + j]);
-      if (e2 < NX) ws[L.q + k * NX + e2] = c.Wq[e2] * (sx[k * NX + e2] - (T)yref[k * NZ + e2]);
-      if (j < NU) {
-        const T uu = su_[k * NU + j];
-        ws[L.r + k * NU + j] = c.Wr[j] * (uu - (T)yref[k * NZ + NX + j]);
-        ws[L.lb + k * NU + j] = c.lbu[j] - uu;
-        ws[L.ubd + k * NU + j] = c.ubu[j] - uu;
-        ws[L.Rt + k * NU + j] = c.Rd[j];
-      }
     }
     const T* pk = pts + k * npts * PT_LD;
     for (int step = 0; step < steps; step++) {
