@@ -587,7 +587,7 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
       *iters = it;
       return ST_QPFAIL;
     }
-    forward_sweep<T, NF>(c, ws, L, sm, lane, T(1), false, true, false, L.kff, L.dx, L.du);
+    forward_sweep<T, NF, false>(c, ws, L, sm, lane, T(1), false, true, false, L.kff, L.dx, L.du);
     PROF_ADD(PH_FWD);
   }
   // box check + interior-point start
@@ -690,7 +690,7 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
       status = (sizeof(T) == 4 && mu <= T(1e-6)) ? ST_SUCCESS : ST_QPFAIL;
       break;
     }
-    forward_sweep<T, NF>(c, ws, L, sm, lane, rq, false, false, false, L.kff, L.dx, L.ua);   // wx = false: no state output
+    forward_sweep<T, NF, false>(c, ws, L, sm, lane, rq, false, false, false, L.kff, L.dx, L.ua);   // wx = false: no state output
     PROF_ADD(PH_FWD);
     // affine step length (division-free ratio test: the running minimum is kept as a fraction
     // an/ad and candidates are compared by cross-multiplication)
@@ -747,7 +747,7 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
     PROF_ADD(PH_ELEM);
     delta_backward<T, NF>(c, ws, L, sm, lane);
     PROF_ADD(PH_DELTA);
-    forward_sweep<T, NF>(c, ws, L, sm, lane, T(0), true, false, false, L.kffd, L.dx, L.ua);
+    forward_sweep<T, NF, false>(c, ws, L, sm, lane, T(0), true, false, false, L.kffd, L.dx, L.ua);
     PROF_ADD(PH_FWD);
     T bn = T(2), bd = T(1);  // ratios >= 2 cannot bind: alpha = min(1, tau * ratio), tau >= 0.995
     bool fin = true;         // NaN anywhere must surface: comparisons drop NaNs, so test explicitly
@@ -825,7 +825,7 @@ __device__ __forceinline__ int ipm_solve(const DevCfg<T>& c, T* __restrict__ ws,
   // input direction, dx_{k+1} = A_k dx_k + B_k du_k + b_k (instead of updating dx every iteration).
   __syncwarp();
   PROF_ADD(PH_ELEM);
-  forward_sweep<T, NF>(c, ws, L, sm, lane, T(1), false, true, true, L.kff, L.dx, L.du);
+  forward_sweep<T, NF, false>(c, ws, L, sm, lane, T(1), false, true, true, L.kff, L.dx, L.du);
   PROF_ADD(PH_FWD);
   *iters = it;
   *ipm_conv = (status == ST_SUCCESS);
@@ -878,11 +878,26 @@ __device__ __forceinline__ bool as_solve(const DevCfg<T>& c, T* __restrict__ ws,
     bool ok = factor_sweep<T, NF, true>(c, ws, L, sm, lane, T(1), any, cj);
     PROF_ADD(PH_FACTOR);
     if (!ok) return false;
-    forward_sweep<T, NF>(c, ws, L, sm, lane, T(1), false, true, false, L.kff, L.dx, L.du);
+#if NMPC_FUSED_MULT
+    // roll-out; it also leaves the multiplier mu = lam_l - lam_u of every fixed input in ws[L.dll]
+    forward_sweep<T, NF, true>(c, ws, L, sm, lane, T(1), false, true, false, L.kff, L.dx, L.du);
+    PROF_ADD(PH_FWD);
+    // the point is the QP solution iff the free rows respect the box and the multipliers of the
+    // fixed rows have the right sign
+    _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
+      const T code = ws[L.dtl + i], du = ws[L.du + i];
+      const T mu = code != T(0) ? ws[L.dll + i] : T(0);
+      ok = ok && (code == T(1) ? (mu >= T(0))
+                               : (code == T(2) ? (-mu >= T(0)) : (du >= ws[L.lb + i] && du <= ws[L.ubd + i])));
+    }
+    ok = __all_sync(FULL, ok);
+#else
+    forward_sweep<T, NF, false>(c, ws, L, sm, lane, T(1), false, true, false, L.kff, L.dx, L.du);
     PROF_ADD(PH_FWD);
     if (any) {
       ok = costate_check<T, NF>(c, ws, L, sm, lane);
       PROF_ADD(PH_DELTA);
+      _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) ws[L.dll + i] -= ws[L.dlu + i];  // mu = lam_l - lam_u
     } else {  // nothing fixed: the point is the solution iff it respects the box
       _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
         const T du = ws[L.du + i];
@@ -890,13 +905,15 @@ __device__ __forceinline__ bool as_solve(const DevCfg<T>& c, T* __restrict__ ws,
       }
       ok = __all_sync(FULL, ok);
     }
+#endif
     if (ok) {  // accepted: slacks / multipliers of this point are the active set and the warm start of the next QP
       _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
         const T code = ws[L.dtl + i], du = ws[L.du + i];
+        const T mu = code != T(0) ? ws[L.dll + i] : T(0);
         ws[L.tl + i] = code == T(1) ? T(0) : du - ws[L.lb + i];
         ws[L.tu + i] = code == T(2) ? T(0) : ws[L.ubd + i] - du;
-        ws[L.ll + i] = any ? ws[L.dll + i] : T(0);
-        ws[L.lu + i] = any ? ws[L.dlu + i] : T(0);
+        ws[L.ll + i] = code == T(1) ? mu : T(0);
+        ws[L.lu + i] = code == T(2) ? -mu : T(0);
       }
       __syncwarp();
       *nact = any;
@@ -910,8 +927,8 @@ __device__ __forceinline__ bool as_solve(const DevCfg<T>& c, T* __restrict__ ws,
       const T code = ws[L.dtl + i], du = ws[L.du + i], lb = ws[L.lb + i], ub = ws[L.ubd + i];
       T ncode = code;
       if (code == T(0)) ncode = du < lb ? T(1) : (du > ub ? T(2) : T(0));
-      else if (any && code == T(1) && !(ws[L.dll + i] >= T(0))) ncode = T(0);
-      else if (any && code == T(2) && !(ws[L.dlu + i] >= T(0))) ncode = T(0);
+      else if (code == T(1) && !(ws[L.dll + i] >= T(0))) ncode = T(0);   // mu = lam_l - lam_u
+      else if (code == T(2) && !(-ws[L.dll + i] >= T(0))) ncode = T(0);
       changed = changed || (ncode != code);
       if (ncode != code) kmax = i >> 2;  // i ascends
       any_new = any_new || (ncode != T(0));
