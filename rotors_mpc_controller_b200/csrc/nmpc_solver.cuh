@@ -882,6 +882,74 @@ __device__ __forceinline__ bool as_solve(const DevCfg<T>& c, T* __restrict__ ws,
     // roll-out; it also leaves the multiplier mu = lam_l - lam_u of every fixed input in ws[L.dll]
     forward_sweep<T, NF, true>(c, ws, L, sm, lane, T(1), false, true, false, L.kff, L.dx, L.du);
     PROF_ADD(PH_FWD);
+#pragma nv_diag_suppress 128   // the run-time-horizon loops below are unreachable in the fixed-horizon instantiation
+    if (NF > 0) {
+      // Fixed horizon: the box rows of a lane (nb / 32, rounded up) fit its registers.  ONE pass of
+      // loads, all in flight together, serves the acceptance test, the slacks / multipliers of an
+      // accepted point and the update of the set (three passes with an L2 round trip per trip in
+      // the run-time-horizon form below).
+      constexpr int NB = (NF > 0 ? NF : 1) * NU, NIT = (NB + 31) / 32;
+      T code[NIT], du[NIT], lbv[NIT], ubv[NIT], mu[NIT];
+#pragma unroll
+      for (int t = 0; t < NIT; t++) {
+        const int i = lane + 32 * t;
+        const bool in = i < NB;
+        code[t] = in ? ws[L.dtl + i] : T(0);
+        du[t] = in ? ws[L.du + i] : T(0);
+        lbv[t] = in ? ws[L.lb + i] : T(-1);
+        ubv[t] = in ? ws[L.ubd + i] : T(1);
+        mu[t] = in ? ws[L.dll + i] : T(0);   // only meaningful where code != 0
+      }
+#pragma unroll
+      for (int t = 0; t < NIT; t++) {
+        const T m_ = code[t] != T(0) ? mu[t] : T(0);
+        ok = ok && (code[t] == T(1) ? (m_ >= T(0))
+                                    : (code[t] == T(2) ? (-m_ >= T(0)) : (du[t] >= lbv[t] && du[t] <= ubv[t])));
+      }
+      ok = __all_sync(FULL, ok);
+      if (ok) {  // accepted, see below
+#pragma unroll
+        for (int t = 0; t < NIT; t++) {
+          const int i = lane + 32 * t;
+          if (i < NB) {
+            const T m_ = code[t] != T(0) ? mu[t] : T(0);
+            ws[L.tl + i] = code[t] == T(1) ? T(0) : du[t] - lbv[t];
+            ws[L.tu + i] = code[t] == T(2) ? T(0) : ubv[t] - du[t];
+            ws[L.ll + i] = code[t] == T(1) ? m_ : T(0);
+            ws[L.lu + i] = code[t] == T(2) ? -m_ : T(0);
+          }
+        }
+        __syncwarp();
+        *nact = any;
+        PROF_ADD(PH_ELEM);
+        return true;
+      }
+      bool changed = false, any_new = false;
+      int kmax = -1;
+#pragma unroll
+      for (int t = 0; t < NIT; t++) {
+        const int i = lane + 32 * t;
+        if (i < NB) {
+          T ncode = code[t];
+          if (code[t] == T(0)) ncode = du[t] < lbv[t] ? T(1) : (du[t] > ubv[t] ? T(2) : T(0));
+          else if (code[t] == T(1) && !(mu[t] >= T(0))) ncode = T(0);
+          else if (code[t] == T(2) && !(-mu[t] >= T(0))) ncode = T(0);
+          changed = changed || (ncode != code[t]);
+          if (ncode != code[t]) kmax = i >> 2;
+          any_new = any_new || (ncode != T(0));
+          ws[L.dtl + i] = ncode;
+          ws[L.dr + i] = ncode == T(1) ? lbv[t] : (ncode == T(2) ? ubv[t] : nan);
+        }
+      }
+      if (!__any_sync(FULL, changed)) return false;
+      any = __any_sync(FULL, any_new);
+      kmax = __reduce_max_sync(FULL, kmax);
+      cj = -1;
+#pragma unroll
+      for (int j = NCK - 1; j >= 0; j--)
+        if (ck_stage(N, j) > kmax && ck_stage(N, j) < N) cj = j;
+      continue;
+    }
     // the point is the QP solution iff the free rows respect the box and the multipliers of the
     // fixed rows have the right sign
     _Pragma("unroll 1") for (int i = lane; i < nb; i += 32) {
