@@ -17,14 +17,19 @@ using namespace nmpc;
 
 namespace {
 
-// CTAs of four independent warps (warps never synchronise with each other; 3 CTAs of 4 x 10.3 KB
-// tiles fit the 132 KB shared-memory configuration).  The register file is partitioned
-// per scheduler (16 K registers each): 3 warps per scheduler = 12 problems in flight per SM fit up
-// to 170 registers, 4 per scheduler need <= 128 (FP32 kernels do, FP64 ones spill in the sweeps and
-// lose more than the extra warps bring).  The FP64 cap is set a little below what ptxas would take
-// (156): the 160-register schedule measures 4-5 % faster than the unconstrained one.
+// CTAs of four independent warps (warps never synchronise with each other; 4 CTAs of 4 x 10.6 KB
+// tiles fit the 196 KB shared-memory configuration).  The register file is partitioned per
+// scheduler (16 K registers each): 4 warps per scheduler = 16 problems in flight per SM need <= 128
+// registers, 3 per scheduler fit up to 170.  History of the FP64 cap: 160 (12 warps per SM) through
+// most of round 2 -- at 128 the sweeps spilled and lost more than the extra warp brought (7.91 vs
+// 7.60 ms on the bench step); once the linearisation and the sweeps had shed their instructions the
+// 128-register build spills 8 bytes and wins (bench 4.73 vs 4.82 ms, large RTI batches +2-4 %).
 #ifndef NMPC_MAXNREG
-#define NMPC_MAXNREG 160
+#define NMPC_MAXNREG 128
+#endif
+// (the run-time-horizon instantiations spill 104 bytes at 128 registers: they keep 160 / 12 warps per SM)
+#ifndef NMPC_MAXNREG_GENERIC
+#define NMPC_MAXNREG_GENERIC 160
 #endif
 #ifndef NMPC_MAXNREG_F32
 #define NMPC_MAXNREG_F32 128
@@ -39,7 +44,7 @@ constexpr int smem_elems_per_warp() { return smem_tile_elems(); }
 // ---------------------------------------------------------------- kernels
 // NF > 0: instantiation for a horizon known at compile time (see fixed_layout); NF = 0: any N.
 template <typename T, int NS, int NF>
-__global__ void __maxnreg__(sizeof(T) == 4 ? NMPC_MAXNREG_F32 : NMPC_MAXNREG)
+__global__ void __maxnreg__(sizeof(T) == 4 ? NMPC_MAXNREG_F32 : (NF > 0 ? NMPC_MAXNREG : NMPC_MAXNREG_GENERIC))
     nmpc_solve_kernel(const __grid_constant__ SolveArgs<T> A, const __grid_constant__ WsLayout Lr,
                       int* __restrict__ work_counter) {
   const WsLayout Lfix_ = NF > 0 ? make_layout(NF > 0 ? NF : 1) : WsLayout();
