@@ -387,13 +387,14 @@ def run_gpu(args):
     tf = C.c_double(0.0)
     peak_fn = _abi.lib().nmpc_fp32_peak if is32 else _abi.lib().nmpc_fp64_peak
     _abi.check(peak_fn(local, C.byref(tf)), 'nmpc_fp32_peak' if is32 else 'nmpc_fp64_peak')
-    traffic, traffic_src = None, None
+    traffic, traffic_src, executed = None, None, None
     try:   # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of this workload's kernel,
            # from the committed `ncu --set full` capture of this very command (written by
            # scripts/ncu_traffic.py; its "source" and "head" fields say which capture and kernel)
         tj = json.load(open(ROOT / 'profiles' / 'traffic.json'))
         if tj.get('dtype', 'f64') == args.dtype:
             traffic, traffic_src = tj['dram_bytes_per_launch'], tj.get('source')
+            executed = tj.get('flops_executed_per_launch')   # thread-level FMA x2 + ADD + MUL of that capture
     except Exception:
         pass
     achieved_gbs = bytes_per_launch / launch_s * 1e-9
@@ -418,7 +419,14 @@ def run_gpu(args):
                                     + ' micro-benchmark on this GPU, same run '
                                     '(MEASURED_PEAKS.json holds no vector-FMA figure)',
                      'flops_per_solve': flops_per_launch / BATCH,
-                     'note': 'algorithmic FP64 flops (DESIGN.md section 5) / CUDA-event launch time'},
+                     'executed_flops_per_solve': executed / BATCH if executed else None,
+                     'note': 'achieved = ALGORITHMIC flops (dense-block count of SURVEY 8d for the '
+                             'reference algorithm: S linearisations + I factorisations with two vector '
+                             'sweeps each, DESIGN.md section 4) / CUDA-event launch time; '
+                             'executed_flops_per_solve = what the kernel really issued in the committed '
+                             'ncu capture (constant Jacobian columns never multiplied, nominal '
+                             'trajectory integrated once per stage, multipliers from the roll-out '
+                             'instead of a costate sweep, checkpoint restarts)'},
         'roofline_hbm': {'bound': 'hbm', 'achieved': achieved_gbs, 'peak': hbm_peak, 'unit': 'GB/s',
                          'frac': achieved_gbs / hbm_peak, 'traffic': traffic,
                          'peak_source': 'MEASURED_PEAKS.json' if peaks else 'fallback',

@@ -32,7 +32,16 @@ def val(k):
 rd, wr = val('dram__bytes_read.sum'), val('dram__bytes_write.sum')
 head = subprocess.run(['git', 'rev-parse', '--short', 'HEAD'], capture_output=True, text=True,
                       cwd=ROOT).stdout.strip()
+def per_cycle(op):
+    k = f'smsp__sass_thread_inst_executed_op_{op}_pred_on.sum.per_cycle_elapsed'
+    return float(d[k][1].replace(',', '')) if k in d else 0.0
+
+
+pre = 'f' if dtype == 'f32' else 'd'
+cycles = float(d['sm__cycles_elapsed.max'][1].replace(',', '')) if 'sm__cycles_elapsed.max' in d else 0.0
+flops_exec = (2.0 * per_cycle(pre + 'fma') + per_cycle(pre + 'add') + per_cycle(pre + 'mul')) * cycles
 out = {
+    'flops_executed_per_launch': flops_exec,   # thread-level FMA x 2 + ADD + MUL (predicated-on), whole launch
     'dram_bytes_per_launch': rd + wr, 'dram_bytes_read': rd, 'dram_bytes_write': wr,
     'lts_sector_hit_rate_pct': float(d['lts__t_sector_hit_rate.pct'][1]),
     'gpu_time_us': float(d['gpu__time_duration.sum'][1].replace(',', '')) *
