@@ -1,21 +1,28 @@
-// nmpc_solver.cuh -- one-warp-per-problem SQP / Riccati interior-point solver, sm_100a.
+// nmpc_solver.cuh -- one-warp-per-problem SQP solver (active-set QP method, Riccati interior point
+// as the fallback), sm_100a.
 //
 // Replaces, for the OCP of /root/reference/src/rotors_mpc_controller/controller.py:175-264,
 // what `solver.solve()` (controller.py:447) runs inside acados: ERK + forward sensitivities,
 // LINEAR_LS Gauss-Newton assembly + Levenberg-Marquardt, the HPIPM QP solve and the full
 // step.  Nothing here is derived from acados / HPIPM sources (they are not in the reference
-// tree); the algorithm is the textbook stage-wise Riccati recursion inside a Mehrotra
-// predictor-corrector, laid out for one warp:
+// tree); the QP methods are a primal-dual active-set method on the input box (as_solve) and the
+// textbook stage-wise Riccati recursion inside a Mehrotra predictor-corrector (ipm_solve), laid
+// out for one warp:
 //
-//   K1 linearise: lane = one sensitivity column of M_k = [B_k | A_k] (14 computed columns, the
-//      two half-warps take two stages at a time); no Jacobian matrix is formed.
+//   K1 linearise: phase A, lane k integrates the nominal state of stage k once; phase B, the
+//      11 N stored sensitivity columns of M_k = [B_k | A_k] (inputs, q, w; the p and v columns are
+//      constants) are dealt out flat over the lanes and evaluate the directional derivative of
+//      the model at the stored points (linearize_points; linearize is the column-per-lane form
+//      for horizons whose points do not fit the tile).  No Jacobian matrix is formed.
 //   K2 factorisation: both half-warps own the 14 computed columns and split the ROWS of
 //      W = P M, G = M'W and of the cost-to-go update (see nmpc_riccati.cuh); P, the cp.async-staged
-//      M_k, K_k and the 4x4 input block go through a per-warp shared-memory tile.
-//   Roll-outs: lanes 0..12 own the rows of M_k, lanes 16..19 the rows of K_k.
-//   Per-stage records [M_k | b_k | K_k], LDL' factors, feed-forwards and all horizon-long
-//   vectors live in a global workspace slot owned by the warp (sized by N, so N = 600 runs
-//   unchanged); per-problem inputs are staged by 1-D TMA bulk copies.
+//      M_k, K_k and the 4x4 input block go through a per-warp shared-memory tile.  Active-set
+//      re-solves restart the recursion from cost-to-go checkpoints (ck_stage).
+//   Roll-outs: lanes 0..12 own the rows of M_k, lanes 16..19 the rows of K_k; the roll-out of an
+//      active-set iteration also delivers the multipliers of the fixed inputs.
+//   Per-stage records [M_k | b_k | K_k | factor slots], feed-forwards, checkpoints and all
+//   horizon-long vectors live in a global workspace slot owned by the warp (sized by N, so
+//   N = 600 runs unchanged); per-problem inputs are staged by 1-D TMA bulk copies.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
