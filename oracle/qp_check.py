@@ -97,3 +97,67 @@ def kkt_residuals(qp, dx, du, lam_l, lam_u):
     comp = max(np.max(np.abs(lam_l * (du - qp['lb']))), np.max(np.abs(lam_u * (qp['ub'] - du))))
     feas = max(np.max(qp['lb'] - du), np.max(du - qp['ub']), 0.0)
     return dict(dyn=dyn, stat=stat, comp=comp, feas=feas, x0=np.max(np.abs(dx[0])))
+
+
+def riccati_active_set(qp, act_l, act_u, restart=None):
+    """numpy restatement of ONE active-set iteration as the CUDA kernel runs it (round 2):
+    backward Riccati recursion with the fixed inputs eliminated, forward roll-out, and the
+    multipliers of the fixed inputs from the derivative of the stage's Q-function at the rolled-out
+    point,  mu_i = Quu(i,:) du_k + Qux(i,:) dx_k + g_u(i)  -- no costate sweep.
+    `restart` = (c, trace of an earlier call): keep the gains of the stages >= c and restart the
+    recursion from the cost-to-go (P_c, p_c) -- the kernel's checkpoints; valid when the two active
+    sets agree on the stages >= c.  Returns (dx, du, lam_l, lam_u, trace), trace = {stage: (P_k, p_k),
+    'K', 'kff', 'keep'}."""
+    A, B, b = qp['A'], qp['B'], qp['b']
+    Qd, Rd, q, r = qp['Q'], qp['R'], qp['q'], qp['r']
+    lb, ub = qp['lb'], qp['ub']
+    N, nx, nu = A.shape[0], A.shape[1], B.shape[2]
+    al, au = np.asarray(act_l, bool), np.asarray(act_u, bool)
+    K, kff = np.zeros((N, nu, nx)), np.zeros((N, nu))
+    keep = {}                      # originals of the stages with a fixed input: Quu, Qux, gu
+    trace = {N: (np.diag(Qd[N]), q[N].copy())}
+    k_hi = N
+    if restart is not None:        # trace of an earlier call + the checkpoint stage
+        k_hi, old = restart
+        P, p = old[k_hi]
+        K[k_hi:], kff[k_hi:] = old['K'][k_hi:], old['kff'][k_hi:]
+        keep.update({k: v for k, v in old['keep'].items() if k >= k_hi})
+        trace[k_hi] = (P.copy(), p.copy())
+    else:
+        P, p = trace[N]
+    for k in range(k_hi - 1, -1, -1):
+        wv = P @ b[k] + p
+        Quu = B[k].T @ P @ B[k] + np.diag(Rd[k])
+        Qux = B[k].T @ P @ A[k]
+        Qxx = A[k].T @ P @ A[k] + np.diag(Qd[k])
+        gu = B[k].T @ wv + r[k]
+        gx = A[k].T @ wv + q[k]
+        fixed = al[k] | au[k]
+        d = np.where(al[k], lb[k], np.where(au[k], ub[k], 0.0))
+        Quu_e, Qux_e, gu_e, gx_e = Quu.copy(), Qux.copy(), gu.copy(), gx.copy()
+        if fixed.any():
+            keep[k] = (Quu.copy(), Qux.copy(), gu.copy())
+            gx_e = gx + Qux[fixed].T @ d[fixed]
+            gu_e = gu + Quu[:, fixed] @ d[fixed]
+            gu_e[fixed] = -d[fixed]
+            Qux_e[fixed] = 0.0
+            Quu_e[fixed, :] = 0.0
+            Quu_e[:, fixed] = 0.0
+            Quu_e[fixed, fixed] = 1.0
+        K[k] = -np.linalg.solve(Quu_e, Qux_e)
+        kff[k] = -np.linalg.solve(Quu_e, gu_e)
+        P = Qxx + Qux_e.T @ K[k]
+        P = 0.5 * (P + P.T)
+        p = gx_e + Qux_e.T @ kff[k]
+        trace[k] = (P.copy(), p.copy())
+    dx, du = np.zeros((N + 1, nx)), np.zeros((N, nu))
+    mu = np.zeros((N, nu))
+    for k in range(N):
+        du[k] = K[k] @ dx[k] + kff[k]
+        dx[k + 1] = A[k] @ dx[k] + B[k] @ du[k] + b[k]
+        if k in keep and (al[k] | au[k]).any():
+            Quu, Qux, gu = keep[k]
+            f = al[k] | au[k]
+            mu[k, f] = (Quu @ du[k] + Qux @ dx[k] + gu)[f]
+    trace['K'], trace['kff'], trace['keep'] = K, kff, keep
+    return dx, du, np.where(al, mu, 0.0), np.where(au, -mu, 0.0), trace

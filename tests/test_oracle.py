@@ -206,6 +206,40 @@ def test_active_set_solve_is_the_exact_kkt_solution(O, cfg):
     assert n_acc >= 10          # every optimal set is accepted (the perturbed ones mostly not)
 
 
+def test_kernel_form_of_the_active_set_iteration(O, cfg):
+    """The CUDA kernel (round 2) runs an active-set iteration differently from the C oracle: the
+    multipliers of the fixed inputs are the derivative of the stage's Q-function at the rolled-out
+    point (no costate sweep), and a re-solve restarts the backward recursion from a cost-to-go
+    checkpoint above the last changed stage.  oracle/qp_check.py::riccati_active_set restates
+    that form in numpy; here it is pinned (a) against the dense KKT solve for the same set --
+    primal point and multipliers -- and (b) restart vs. full sweep: identical to the bit."""
+    from oracle import qp_check as Q
+    rng = np.random.default_rng(12)
+    n_fixed = 0
+    for qp in _qp_cases(O, cfg, rng, 8, cold=False):
+        N = qp['A'].shape[0]
+        s = O.qp_solve(qp)
+        al = s['lam_l'] > (s['du'] - qp['lb'])
+        au = s['lam_u'] > (qp['ub'] - s['du'])
+        n_fixed += int(al.sum() + au.sum())
+        dx, du, ll, lu, tr = Q.riccati_active_set(qp, al, au)
+        dxk, duk, llk, luk = Q.active_set_kkt(qp, al, au)
+        assert np.max(np.abs(du - duk)) < 1e-10 and np.max(np.abs(dx - dxk)) < 1e-10
+        assert np.max(np.abs(ll - llk)) < 1e-9 and np.max(np.abs(lu - luk)) < 1e-9
+        # change the set at stages 0..2 only and restart from the checkpoint at stage 4 (N / 5)
+        al2, au2 = al.copy(), au.copy()
+        al2[0, 1], au2[0, 1] = not al2[0, 1], False
+        al2[2, 3], au2[2, 3] = False, not au2[2, 3]
+        full = Q.riccati_active_set(qp, al2, au2)
+        part = Q.riccati_active_set(qp, al2, au2, restart=(N // 5, tr))
+        for a, b in zip(full[:4], part[:4]):
+            assert np.array_equal(a, b)
+        dxk, duk, llk, luk = Q.active_set_kkt(qp, al2, au2)
+        assert np.max(np.abs(part[1] - duk)) < 1e-10
+        assert np.max(np.abs(part[2] - llk)) < 1e-9 and np.max(np.abs(part[3] - luk)) < 1e-9
+    assert n_fixed > 20
+
+
 @pytest.mark.parametrize('kind', ['cfg2_sqp', 'aggressive_rti'])
 def test_active_set_method_matches_interior_point(O, params, kind):
     """as_shortcut on / off in the oracle: same statuses, same SQP iteration behaviour, u0 within the
