@@ -164,7 +164,7 @@ int nmpc_solve_device(nmpc_handle_t *h, const double *x0, const double *yref, co
  *   u0, status, thrust, speed, qp_iters, sqp_iters   outputs, device, any may be NULL
  * Limits (NMPC_E_INVALID + nmpc_last_error() beyond them): 1 <= batch <= NMPC_STATIC_MAX_BATCH, and
  * a horizon whose four per-warp workspaces (one CTA) fit the scratch array (N <= 600 in FP64 does).
- * The number of problems in flight is what fits the array (N = 20, FP64: 148 CTAs x 4 warps);
+ * The number of problems in flight is what fits the array (N = 20, FP64: 156 CTAs x 4 warps);
  * problems are handed out in index order.  The per-problem rows are read with plain loads, so the
  * caller's buffers need no padding and only 8-byte alignment.
  * ALL calls on one GPU share the array: calls that overlap on the GPU (different streams or

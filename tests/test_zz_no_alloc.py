@@ -93,7 +93,7 @@ def _two_calls(params, B, N, seed, scenario):
 
 
 def test_static_rti_reference_configuration(params, built):
-    """configs[0] (the reference's RTI step, N = 20, FP64); batch above the 592 warps the scratch
+    """configs[0] (the reference's RTI step, N = 20, FP64); batch above the 624 warps the scratch
     array holds at N = 20, so the work queue hands out several problems per warp."""
     _two_calls(params, 2500, 20, 11, 'aggressive')
 
